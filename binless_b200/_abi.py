@@ -1,0 +1,283 @@
+"""ctypes mirror of include/fastbinless.h (structs + a thin caller).
+
+``FastBinlessLib(path, prefix)`` binds one shared library that exports the C ABI
+under ``prefix`` (``fb_`` for the CUDA product library). It performs the same
+marshalling the Rcpp shim does: numpy columns in, freshly
+allocated numpy columns out. No computation happens in Python.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import numpy as np
+
+FB_DECAY_K = 50
+FB_MAX_OUTER = 256
+
+c_dp = C.POINTER(C.c_double)
+c_ip = C.POINTER(C.c_int32)
+
+
+class fb_mat(C.Structure):
+    _fields_ = [("N", C.c_int64), ("name", c_ip), ("bin1", c_ip), ("pos1", c_ip), ("bin2", c_ip),
+                ("pos2", c_ip), ("observed", c_ip), ("nobs", c_ip), ("distance", c_dp)]
+
+
+class fb_params(C.Structure):
+    _fields_ = [("alpha", C.c_double), ("lam2", c_dp), ("n_lam2", C.c_int), ("lam1", c_dp),
+                ("n_lam1", C.c_int), ("nouter", C.c_uint), ("tol_val", C.c_double),
+                ("bg_steps", C.c_uint), ("free_decay", C.c_uint), ("compute_patchnos", C.c_int),
+                ("csv_out", C.c_char_p), ("maxdiag", C.c_uint), ("verbose", C.c_int)]
+
+
+class fb_mean_state(C.Structure):
+    _fields_ = [("estimate", c_dp), ("n", C.c_int), ("mean", C.c_double)]
+
+
+class fb_gam_state(C.Structure):
+    _fields_ = [("beta", C.c_double * FB_DECAY_K), ("lambda_", C.c_double), ("mean", C.c_double)]
+
+
+class fb_signal_out(C.Structure):
+    _fields_ = [("background", c_dp), ("biasmat", c_dp), ("decaymat", c_dp), ("signal", c_dp),
+                ("binless", c_dp), ("phihat", c_dp), ("weight", c_dp), ("patchno", c_ip),
+                ("log_signal", c_dp), ("biases", fb_mean_state), ("decay", fb_gam_state),
+                ("exposures", fb_mean_state), ("nsteps", C.c_int), ("converged", C.c_int),
+                ("prec_abs", C.c_double * FB_MAX_OUTER), ("prec_rel", C.c_double * FB_MAX_OUTER),
+                ("admm_iters", C.c_int64), ("admm_cell_iters", C.c_int64), ("n_solves", C.c_int64),
+                ("solve_iters", c_ip), ("solve_iters_cap", C.c_int64),
+                ("ms_total", C.c_double), ("ms_solver", C.c_double)]
+
+
+class fb_diff_out(C.Structure):
+    _fields_ = [("difference", c_dp), ("deltahat", c_dp), ("weight", c_dp), ("phi_ref", c_dp),
+                ("patchno", c_ip), ("admm_iters", C.c_int64), ("admm_cell_iters", C.c_int64),
+                ("n_solves", C.c_int64), ("solve_iters", c_ip), ("solve_iters_cap", C.c_int64),
+                ("ms_total", C.c_double), ("ms_solver", C.c_double)]
+
+
+class fb_cv_out(C.Structure):
+    _fields_ = [("signal", c_dp), ("binless", c_dp), ("phihat", c_dp), ("weight", c_dp),
+                ("log_signal", c_dp), ("patchno", c_ip)]
+
+
+class fb_gfl_state(C.Structure):
+    _fields_ = [("beta", c_dp), ("z", c_dp), ("u", c_dp), ("alpha", C.c_double), ("steps", C.c_int)]
+
+
+ENTRY_POINTS = ["create", "destroy", "last_error", "run_signal", "restore", "run_difference",
+                "eval_cv", "gfl_solve", "set_interrupt_cb"]
+
+
+def _dp(a):
+    return a.ctypes.data_as(c_dp) if a is not None else None
+
+
+def _ip(a):
+    return a.ctypes.data_as(c_ip) if a is not None else None
+
+
+def _i32(a):
+    return np.ascontiguousarray(a, dtype=np.int32)
+
+
+def _f64(a):
+    return np.ascontiguousarray(a, dtype=np.float64)
+
+
+class FastBinlessError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(msg)
+        self.code = code
+
+
+class FastBinlessLib:
+    """One loaded library exporting the fastbinless C ABI under ``prefix``."""
+
+    def __init__(self, path: str, prefix: str = "fb_"):
+        self.path = path
+        self.prefix = prefix
+        self.lib = C.CDLL(path)
+        f = lambda n: getattr(self.lib, prefix + n)
+        self._create = f("create")
+        self._create.argtypes = [C.c_int, C.POINTER(fb_mat), C.POINTER(C.c_void_p)]
+        self._create.restype = C.c_int
+        self._destroy = f("destroy"); self._destroy.argtypes = [C.c_void_p]; self._destroy.restype = None
+        self._last_error = f("last_error"); self._last_error.argtypes = [C.c_void_p]; self._last_error.restype = C.c_char_p
+        self._run_signal = f("run_signal")
+        self._run_signal.argtypes = [C.c_void_p, C.POINTER(fb_params), C.POINTER(fb_signal_out)]
+        self._run_signal.restype = C.c_int
+        self._restore = f("restore")
+        self._restore.argtypes = [C.c_void_p, c_dp, C.POINTER(fb_mean_state), C.POINTER(fb_gam_state), C.POINTER(fb_mean_state)]
+        self._restore.restype = C.c_int
+        self._run_difference = f("run_difference")
+        self._run_difference.argtypes = [C.c_void_p, C.c_int, C.POINTER(fb_params), C.POINTER(fb_diff_out)]
+        self._run_difference.restype = C.c_int
+        self._eval_cv = f("eval_cv")
+        self._eval_cv.argtypes = [C.c_void_p, C.POINTER(fb_params), C.c_int, c_dp, C.c_uint, C.POINTER(fb_cv_out)]
+        self._eval_cv.restype = C.c_int
+        self._gfl_solve = f("gfl_solve")
+        self._gfl_solve.argtypes = [C.c_int, C.c_uint, c_dp, c_dp, C.c_double, C.c_double, C.c_int, C.c_int,
+                                    C.POINTER(fb_gfl_state), c_dp]
+        self._gfl_solve.restype = C.c_int
+
+    # ---- helpers -------------------------------------------------------
+    def _check(self, rc, h=None):
+        if rc != 0:
+            msg = self._last_error(h)
+            raise FastBinlessError(rc, (msg or b"unknown error").decode())
+
+    @staticmethod
+    def _params(alpha, lam2, lam1, nouter=25, tol_val=0.2, bg_steps=5, free_decay=10000,
+                compute_patchnos=True, csv_out="", maxdiag=0, verbose=False):
+        lam2a = _f64(np.atleast_1d(lam2)); lam1a = _f64(np.atleast_1d(lam1))
+        p = fb_params(alpha=float(alpha), lam2=_dp(lam2a), n_lam2=lam2a.size, lam1=_dp(lam1a),
+                      n_lam1=lam1a.size, nouter=int(nouter), tol_val=float(tol_val), bg_steps=int(bg_steps),
+                      free_decay=int(free_decay), compute_patchnos=int(bool(compute_patchnos)),
+                      csv_out=(csv_out or "").encode(), maxdiag=int(maxdiag), verbose=int(bool(verbose)))
+        p._keep = (lam2a, lam1a)
+        return p
+
+    def create(self, mat, nbins):
+        cols = {}
+        for k in ("name", "bin1", "pos1", "bin2", "pos2", "observed", "nobs"):
+            cols[k] = _i32(mat[k]) if mat.get(k) is not None else None
+        cols["distance"] = _f64(mat["distance"])
+        m = fb_mat(N=cols["distance"].size, distance=_dp(cols["distance"]),
+                   **{k: _ip(v) for k, v in cols.items() if k != "distance"})
+        h = C.c_void_p()
+        rc = self._create(int(nbins), C.byref(m), C.byref(h))
+        self._check(rc, None)
+        return Handle(self, h, cols, int(nbins))
+
+
+class Handle:
+    """An fb_handle plus the host columns it was created from."""
+
+    def __init__(self, lib: FastBinlessLib, h, cols, nbins):
+        self.lib, self.h, self.cols, self.nbins = lib, h, cols, nbins
+        self.N = cols["distance"].size
+        self.ncells = nbins * (nbins + 1) // 2
+        self.ndatasets = self.N // self.ncells
+
+    def close(self):
+        if self.h:
+            self.lib._destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def run_signal(self, alpha, lam2, lam1=0.0, columns=True, **kw):
+        p = self.lib._params(alpha, lam2, lam1, **kw)
+        N = self.N
+        names = ("background", "biasmat", "decaymat", "signal", "binless", "phihat", "weight")
+        arr = {k: np.empty(N) for k in names} if columns else {}
+        patch = np.empty(N, dtype=np.int32) if columns else None
+        log_signal = np.empty(N)
+        b_est = np.empty(self.nbins); e_est = np.empty(self.ndatasets)
+        cap = max(1, self.ndatasets * int(p.nouter))
+        iters = np.zeros(cap, dtype=np.int32)
+        out = fb_signal_out(patchno=_ip(patch), log_signal=_dp(log_signal),
+                            solve_iters=_ip(iters), solve_iters_cap=cap,
+                            **{k: _dp(v) for k, v in arr.items()})
+        out.biases.estimate = _dp(b_est); out.biases.n = self.nbins
+        out.exposures.estimate = _dp(e_est); out.exposures.n = self.ndatasets
+        rc = self.lib._run_signal(self.h, C.byref(p), C.byref(out))
+        self.lib._check(rc, self.h)
+        res = dict(arr)
+        if columns:
+            res["patchno"] = patch
+        res.update(log_signal=log_signal,
+                   biases=dict(estimate=b_est[:out.biases.n].copy(), mean=out.biases.mean),
+                   decay=dict(beta=np.array(out.decay.beta[:]), lambda_=out.decay.lambda_, mean=out.decay.mean),
+                   exposures=dict(estimate=e_est[:out.exposures.n].copy(), mean=out.exposures.mean),
+                   nbins=self.nbins,
+                   diagnostics=dict(nsteps=out.nsteps, converged=bool(out.converged),
+                                    prec_abs=np.array(out.prec_abs[:min(out.nsteps, FB_MAX_OUTER)]),
+                                    prec_rel=np.array(out.prec_rel[:min(out.nsteps, FB_MAX_OUTER)]),
+                                    admm_iters=out.admm_iters, admm_cell_iters=out.admm_cell_iters,
+                                    n_solves=out.n_solves, solve_iters=iters[:out.n_solves].copy(),
+                                    ms_total=out.ms_total, ms_solver=out.ms_solver))
+        return res
+
+    def restore(self, log_signal, biases, decay, exposures):
+        ls = _f64(log_signal)
+        be = _f64(biases["estimate"]); ee = _f64(exposures["estimate"])
+        bs = fb_mean_state(estimate=_dp(be), n=be.size, mean=float(biases["mean"]))
+        es = fb_mean_state(estimate=_dp(ee), n=ee.size, mean=float(exposures["mean"]))
+        gs = fb_gam_state(lambda_=float(decay["lambda_"]), mean=float(decay["mean"]))
+        for i, v in enumerate(np.asarray(decay["beta"], dtype=np.float64)):
+            gs.beta[i] = v
+        rc = self.lib._restore(self.h, _dp(ls), C.byref(bs), C.byref(gs), C.byref(es))
+        self.lib._check(rc, self.h)
+
+    def run_difference(self, ref, alpha, lam2, lam1=0.0, tol_val=0.2, compute_patchnos=True, maxdiag=0, verbose=False):
+        p = self.lib._params(alpha, lam2, lam1, tol_val=tol_val, compute_patchnos=compute_patchnos,
+                             maxdiag=maxdiag, verbose=verbose)
+        N = self.N
+        arr = {k: np.empty(N) for k in ("difference", "deltahat", "weight", "phi_ref")}
+        patch = np.empty(N, dtype=np.int32)
+        cap = max(1, self.ndatasets)
+        iters = np.zeros(cap, dtype=np.int32)
+        out = fb_diff_out(patchno=_ip(patch), solve_iters=_ip(iters), solve_iters_cap=cap,
+                          **{k: _dp(v) for k, v in arr.items()})
+        rc = self.lib._run_difference(self.h, int(ref), C.byref(p), C.byref(out))
+        self.lib._check(rc, self.h)
+        res = dict(arr); res["patchno"] = patch
+        res["diagnostics"] = dict(admm_iters=out.admm_iters, admm_cell_iters=out.admm_cell_iters,
+                                  n_solves=out.n_solves, solve_iters=iters[:out.n_solves].copy(),
+                                  ms_total=out.ms_total, ms_solver=out.ms_solver)
+        return res
+
+    def eval_cv(self, alpha, lam2, lam1=0.0, group=0, tol_val=0.1, maxdiag=0):
+        lam2a = _f64(np.atleast_1d(lam2))
+        p = self.lib._params(alpha, lam2a, lam1, tol_val=tol_val, maxdiag=maxdiag)
+        N = self.N
+        outs = (fb_cv_out * lam2a.size)()
+        keep = []
+        for o in outs:
+            a = {k: np.empty(N) for k in ("signal", "binless", "phihat", "weight", "log_signal")}
+            pt = np.empty(N, dtype=np.int32)
+            for k, v in a.items():
+                setattr(o, k, _dp(v))
+            o.patchno = _ip(pt)
+            a["patchno"] = pt
+            keep.append(a)
+        rc = self.lib._eval_cv(self.h, C.byref(p), lam2a.size, _dp(lam2a), int(group), outs)
+        self.lib._check(rc, self.h)
+        return keep
+
+
+def gfl_solve(lib: FastBinlessLib, nbins, y, w, lam2, converge, maxsteps=30000, maxdiag=0, state=None):
+    """FusedLassoGaussianEstimator<GFLLibrary>::optimize on one packed triangle."""
+    y = _f64(y); w = _f64(w)
+    nc = nbins * (nbins + 1) // 2
+    md = min(int(maxdiag), nbins)
+    if md > (nbins + 1) // 2 or md <= 1:
+        n_solved = nc
+        tsz = 2 * nc - 2
+    else:
+        n_solved = md * (nbins - md + 1) + (md - 1) * md // 2
+        nrow_tr = sum(1 for i in range(nbins) if min(md, nbins - i) >= 2)
+        tsz = (n_solved - (nbins - nrow_tr)) + (n_solved - 1)
+    warm = state is not None
+    if warm:
+        beta = _f64(state["beta"]).copy(); z = _f64(state["z"]).copy(); u = _f64(state["u"]).copy()
+        alpha = float(state["alpha"])
+    else:
+        beta = np.zeros(n_solved); z = np.zeros(tsz); u = np.zeros(tsz); alpha = 5.0
+    st = fb_gfl_state(beta=_dp(beta), z=_dp(z), u=_dp(u), alpha=alpha, steps=0)
+    full = np.empty(nc)
+    rc = lib._gfl_solve(int(nbins), int(maxdiag), _dp(y), _dp(w), float(lam2), float(converge), int(maxsteps),
+                        int(warm), C.byref(st), _dp(full))
+    lib._check(rc, None)
+    return dict(beta=beta, z=z, u=u, alpha=st.alpha, steps=st.steps, beta_full=full)

@@ -1,0 +1,182 @@
+/*
+ * fastbinless.h -- C ABI of the B200-native fast-binless library
+ * (libfastbinless_cuda.so).
+ *
+ * This is the drop-in boundary for the two R entry points that the reference
+ * registers in RCPP_MODULE(binless_cpp):
+ *
+ *   fast_binless            -> binless::fast::binless()
+ *                              /root/reference/binless/src/csnorm_cpp.cpp:18-22,
+ *                              /root/reference/binless/src/fast_binless.cpp:85-184
+ *   fast_binless_difference -> binless::fast::binless_difference()
+ *                              csnorm_cpp.cpp:23-26, fast_binless.cpp:235-279
+ *   (binless_eval_cv, fast_binless.cpp:186-233, exists in the reference's C++
+ *    but is not registered with R; fb_eval_cv exposes it.)
+ *
+ * An Rcpp shim (r/fastbinless_shim.cpp) converts the R
+ * DataFrame / List arguments to the plain buffers below and back, so the R
+ * signatures and the returned list / data-frame layout stay unchanged.
+ *
+ * Conventions
+ *   - Plain pointers and sizes only. The caller owns every host buffer passed
+ *     in or out; the library owns all device memory behind fb_handle.
+ *   - Every function returns 0 on success; non-zero means failure and
+ *     fb_last_error() gives the message the shim hands to Rcpp::stop().
+ *   - There is no CPU fallback: without a CUDA device every compute entry
+ *     point fails with FB_ERR_CUDA.
+ *   - Input layout is the one FastDataCore requires
+ *     (/root/reference/binless/src/FastData.ipp:3-26): N = ndatasets *
+ *     nbins*(nbins+1)/2 rows sorted by (name, bin1, bin2), i.e. dataset-major
+ *     packed upper triangles in row-major order.
+ */
+#ifndef FASTBINLESS_H
+#define FASTBINLESS_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#ifndef FB_API
+#define FB_API __attribute__((visibility("default")))
+#endif
+
+/* Allow the CPU oracle (test infrastructure) to export the same ABI under a
+ * different prefix (fbo_*) so tests drive both through identical structs. */
+#ifndef FB_NAME
+#define FB_NAME(x) fb_##x
+#endif
+
+enum {
+    FB_OK = 0,
+    FB_ERR_ARG = 1,     /* invalid argument: message mirrors the reference's Rcpp::stop text */
+    FB_ERR_CUDA = 2,    /* CUDA runtime failure or no device */
+    FB_ERR_STATE = 3,   /* call order violation (e.g. difference before signal/restore) */
+    FB_ERR_NUMERIC = 4, /* e.g. "decomposition failed" (QuadProgGAMLibrary.cpp:21) */
+    FB_ERR_INTERRUPT = 5
+};
+
+#define FB_DECAY_K 50       /* Config<Decay,GAM>::K, fast_decay.hpp:25 */
+#define FB_MAX_OUTER 256    /* capacity of the per-step diagnostic arrays */
+
+typedef struct fb_handle fb_handle;
+
+/* The `mat` data frame handed to fast_binless (columns of FastDataCore,
+ * FastData.ipp:5-14). name/bin1/bin2 may be NULL, meaning the canonical order;
+ * when given they are validated like the reference does. */
+typedef struct {
+    int64_t N;
+    const int32_t *name, *bin1, *pos1, *bin2, *pos2;
+    const int32_t *observed, *nobs;
+    const double *distance;
+} fb_mat;
+
+/* Arguments of fast_binless / fast_binless_difference that are not data
+ * (fast_binless.hpp:29-38; defaults csnorm_cpp.cpp:19-25). */
+typedef struct {
+    double alpha;
+    const double *lam2; int n_lam2;   /* broadcast lam2[0] unless n_lam2 == number of solves */
+    const double *lam1; int n_lam1;   /* NULL/0 means lam1 = 0 */
+    unsigned nouter;                  /* default 25 */
+    double tol_val;                   /* default 0.2 */
+    unsigned bg_steps;                /* default 5 */
+    unsigned free_decay;              /* default 10000 */
+    int compute_patchnos;             /* default 1 */
+    const char *csv_out;              /* default "" (NULL allowed) */
+    unsigned maxdiag;                 /* default 0 = full triangle */
+    int verbose;                      /* 1: print the reference's progress lines to stdout */
+} fb_params;
+
+/* State of one Mean leg (Params<Mean>, fast_fitter_mean.hpp:15-33) */
+typedef struct { double *estimate; int n; double mean; } fb_mean_state;
+/* State of the GAM decay leg (Params<GAM>, fast_fitter_gam.hpp:17-41) */
+typedef struct { double beta[FB_DECAY_K]; double lambda; double mean; } fb_gam_state;
+
+/* Outputs of fast_binless: the 16-column `mat` data frame minus the 8 input
+ * columns (fast_dataframe.cpp:90-105) plus the list members biases / decay /
+ * exposures / log_signal (fast_binless.cpp:179-183). All arrays are caller
+ * allocated with N entries unless stated; any pointer may be NULL to skip
+ * that column. */
+typedef struct {
+    double *background, *biasmat, *decaymat, *signal, *binless, *phihat, *weight;
+    int32_t *patchno;            /* -1 everywhere when compute_patchnos == 0 */
+    double *log_signal;
+    fb_mean_state biases;        /* estimate has nbins entries */
+    fb_gam_state decay;
+    fb_mean_state exposures;     /* estimate has ndatasets entries */
+    /* diagnostics (not part of the R return value) */
+    int nsteps;                  /* outer steps performed */
+    int converged;
+    double prec_abs[FB_MAX_OUTER], prec_rel[FB_MAX_OUTER]; /* "reached precision" per step */
+    int64_t admm_iters;          /* total ADMM iterations over all solves */
+    int64_t admm_cell_iters;     /* sum over solves of cells_solved * iterations */
+    int64_t n_solves;
+    int32_t *solve_iters;        /* optional: iterations of each solve, in call order */
+    int64_t solve_iters_cap;
+    double ms_total, ms_solver;  /* device-timed, for benchmarking */
+} fb_signal_out;
+
+/* Outputs of fast_binless_difference: the 12-column data frame minus the 7
+ * input columns (fast_dataframe.cpp:133-144). */
+typedef struct {
+    double *difference, *deltahat, *weight, *phi_ref;
+    int32_t *patchno;
+    int64_t admm_iters, admm_cell_iters, n_solves;
+    int32_t *solve_iters; int64_t solve_iters_cap;
+    double ms_total, ms_solver;
+} fb_diff_out;
+
+/* One element of the list binless_eval_cv returns (fast_binless.cpp:215-229):
+ * the `mat` columns for one lambda2. Arrays have N entries. */
+typedef struct {
+    double *signal, *binless, *phihat, *weight, *log_signal;
+    int32_t *patchno;
+} fb_cv_out;
+
+/* FastDataCore constructor (FastData.ipp:3-26): validates and uploads. */
+FB_API int FB_NAME(create)(int nbins, const fb_mat *mat, fb_handle **out);
+FB_API void FB_NAME(destroy)(fb_handle *h);
+FB_API const char *FB_NAME(last_error)(const fb_handle *h); /* h may be NULL: last create error */
+
+/* fast_binless (fast_binless.cpp:85-184) */
+FB_API int FB_NAME(run_signal)(fb_handle *h, const fb_params *p, fb_signal_out *out);
+
+/* Rebuild estimators from a saved fast_binless result, as binless_difference
+ * and binless_eval_cv do with set_state (fast_binless.cpp:244-260). */
+FB_API int FB_NAME(restore)(fb_handle *h, const double *log_signal,
+                            const fb_mean_state *biases, const fb_gam_state *decay,
+                            const fb_mean_state *exposures);
+
+/* fast_binless_difference (fast_binless.cpp:235-279); ref is 1-based. */
+FB_API int FB_NAME(run_difference)(fb_handle *h, int ref, const fb_params *p, fb_diff_out *out);
+
+/* binless_eval_cv (fast_binless.cpp:186-233): one dataset, nlam lambda2 values
+ * evaluated in order with the warm-start chain of the reference; group is the
+ * checkerboard hold-out group (0 = none). outs[nlam]. */
+FB_API int FB_NAME(eval_cv)(fb_handle *h, const fb_params *p, int nlam, const double *lam2,
+                            unsigned group, fb_cv_out *outs);
+
+/* Stand-alone fused-lasso solve on the triangle grid (the
+ * FusedLassoGaussianEstimator<GFLLibrary> object of the reference,
+ * FusedLassoGaussianEstimator.hpp:16-71, GFLLibraryTriangleImpl.cpp:60-71).
+ * Used by the lambda2/BIC sweep and by the solver benchmarks: y, w, beta are
+ * packed triangles of nbins*(nbins+1)/2 cells; state 0 = cold start, otherwise
+ * z/u/alpha are read and written back (trail-slot order of the reference:
+ * rows then columns, tsz = 2*ncells-2 entries, or the trapeze order). */
+typedef struct {
+    double *beta;       /* in (warm) / out, ncells of the solved grid */
+    double *z, *u;      /* in/out, tsz entries, may be NULL for cold start + discard */
+    double alpha;       /* in/out */
+    int steps;          /* out: return value of graph_fused_lasso_weight_warm */
+} fb_gfl_state;
+FB_API int FB_NAME(gfl_solve)(int nbins, unsigned maxdiag, const double *y, const double *w,
+                              double lam2, double converge, int maxsteps, int warm,
+                              fb_gfl_state *st, double *beta_full);
+
+FB_API int FB_NAME(set_interrupt_cb)(fb_handle *h, int (*cb)(void *), void *arg);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FASTBINLESS_H */
