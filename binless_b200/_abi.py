@@ -97,7 +97,13 @@ class FastBinlessLib:
         self.path = path
         self.prefix = prefix
         self.lib = C.CDLL(path)
-        f = lambda n: getattr(self.lib, prefix + n)
+        def f(n):
+            try:
+                return getattr(self.lib, prefix + n)
+            except AttributeError:  # a partial library (development builds): fail at call time
+                def missing(*a, **k):
+                    raise FastBinlessError(-1, f"{path} does not export {prefix}{n}")
+                return missing
         self._create = f("create")
         self._create.argtypes = [C.c_int, C.POINTER(fb_mat), C.POINTER(C.c_void_p)]
         self._create.restype = C.c_int

@@ -1,0 +1,103 @@
+// fb_gfl.cuh -- graph-fused-lasso ADMM solver on the triangle / band grid (device-resident).
+//
+// Replaces, on the GPU, what the reference does in
+//   FusedLassoGaussianEstimator<GFLLibrary>            FusedLassoGaussianEstimator.hpp:16-71
+//   GFLLibraryTriangleImpl / GFLLibraryTrapezeImpl     GFLLibraryTriangleImpl.cpp, GFLLibraryTrapezeImpl.cpp
+//   graph_fused_lasso_weight_warm + update_*           gfl_graph_fl.c:53-365
+//   tf_dp_weight                                       gfl_tf.c:184-321
+// (paths relative to /root/reference/binless/src). See DESIGN.md for the layout.
+#pragma once
+#include "fb_util.cuh"
+
+namespace fb {
+
+// Geometry of the solved grid: upper-triangular band of width md (md == n is the
+// full triangle). Cells (i,j), 0 <= j-i < md.
+//   "rm" = row-major packed (row i contiguous), "cm" = column-major packed.
+struct Grid {
+    int n = 0, md = 0;
+    int nfull = 0;          // rows holding md cells
+    int64_t ncells = 0;     // cells in the band
+    __host__ __device__ __forceinline__ int row_len(int i) const { return min_(md, n - i); }
+    __host__ __device__ __forceinline__ int col_len(int j) const { return min_(md, j + 1); }
+    __host__ __device__ __forceinline__ int col_first_row(int j) const { return j + 1 - col_len(j); }
+    __host__ __device__ __forceinline__ int64_t rm_row_start(int64_t i) const {
+        if (i <= nfull) return i * md;
+        // rows nfull..i-1 hold n-k cells
+        return (int64_t)nfull * md + (i - nfull) * (int64_t)n - (i * (i - 1) - (int64_t)nfull * (nfull - 1)) / 2;
+    }
+    __host__ __device__ __forceinline__ int64_t cm_col_start(int64_t j) const {
+        if (j < md) return (j * (j + 1)) / 2;
+        return ((int64_t)md * (md + 1)) / 2 + (j - md) * (int64_t)md;
+    }
+    __host__ __device__ __forceinline__ int64_t rm(int i, int j) const { return rm_row_start(i) + (j - i); }
+    __host__ __device__ __forceinline__ int64_t cm(int i, int j) const { return cm_col_start(j) + (i - col_first_row(j)); }
+    __host__ __device__ __forceinline__ int nchains() const { return 2 * (n - 1); }
+    // chain q: even -> row q/2, odd -> column n-1-q/2 (equal lengths, long first)
+    __host__ __device__ __forceinline__ void chain(int q, int &dir, int &idx, int &len, int64_t &start) const {
+        int r = q >> 1;
+        if ((q & 1) == 0) { dir = 0; idx = r; len = row_len(r); start = rm_row_start(r); }
+        else { dir = 1; idx = n - 1 - r; len = col_len(idx); start = cm_col_start(idx); }
+    }
+    static __host__ __device__ __forceinline__ int min_(int a, int b) { return a < b ? a : b; }
+    static Grid make(int n, int md) {
+        Grid g; g.n = n; g.md = md; g.nfull = n - md + 1;
+        g.ncells = (int64_t)md * (n - md + 1) + ((int64_t)(md - 1) * md) / 2;
+        return g;
+    }
+};
+
+// Device-resident control block of one ADMM solve.
+struct GflCtl {
+    double alpha, lam, converge, inflate;
+    double presnorm, dresnorm;
+    int step, maxsteps, done;
+    int rescale;      // pending dual rescale: 0 none, 1 u /= inflate, 2 u *= inflate
+};
+
+// One GFLLibrary strategy object: persistent beta / z / u / alpha (warm start)
+// living in HBM. y and w are device pointers to ncells_tri packed (row-major)
+// values of ONE dataset in the FULL triangle; for a band they are gathered.
+class GflSolver {
+public:
+    GflSolver(int nbins, unsigned maxdiag, cudaStream_t stream);
+    ~GflSolver();
+    void reset();                      // cold start (GFLLibraryTriangleImpl::reset)
+    // runs ADMM to convergence; returns `step` like graph_fused_lasso_weight_warm
+    int optimize(const double *d_y_tri, const double *d_w_tri, double lam2, double converge);
+    // clamp(+-50) of the solution scattered to the full packed triangle
+    // (FusedLassoGaussianEstimator::get + fill_triangle); out has n(n+1)/2 entries
+    void get_beta_full(double *d_out_tri);
+    // state import/export in the reference's trail-slot order
+    void export_state(double *h_beta, double *h_z, double *h_u) ;
+    void import_state(const double *h_beta, const double *h_z, const double *h_u);
+
+    bool trapeze() const { return trapeze_; }
+    const Grid &grid() const { return g_; }
+    int64_t tsz() const { return 2 * g_.ncells - 2; }
+    double alpha = 5.0;                // Settings<GFLLibraryImpl>::get_alpha
+    double inflate = 2.0;
+    int ninner_max = 30000;
+    unsigned counter = 0;
+    int last_steps = 0;
+    float ms_last = 0.f;               // device time of the last optimize()
+    int64_t kernel_launches = 0;
+
+private:
+    Grid g_;
+    int nbins_;
+    bool trapeze_;
+    cudaStream_t st_;
+    DevBuf<double> beta_, yr_, yc_, zr_, ur_, zc_, uc_, mr_, mc_, yband_, wband_, fillavg_;
+    DevBuf<uint32_t> flags_;           // [2 parities][2 directions][nwords]
+    DevBuf<double> partials_;
+    DevBuf<GflCtl> ctl_;
+    GflCtl *h_ctl_ = nullptr;          // pinned
+    const double *y_tri_ = nullptr, *w_tri_ = nullptr;
+    int64_t nwords_ = 0;
+    int n_partials_ = 0;
+    cudaEvent_t ev0_, ev1_;
+    void iteration(const double *y, const double *w, int parity);
+};
+
+} // namespace fb
