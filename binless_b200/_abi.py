@@ -65,7 +65,7 @@ class fb_gfl_state(C.Structure):
 
 
 ENTRY_POINTS = ["create", "destroy", "last_error", "run_signal", "restore", "run_difference",
-                "eval_cv", "gfl_solve", "set_interrupt_cb"]
+                "eval_cv", "gfl_solve", "set_interrupt_cb", "kernel_launches"]
 
 
 def _dp(a):
@@ -121,6 +121,8 @@ class FastBinlessLib:
         self._eval_cv = f("eval_cv")
         self._eval_cv.argtypes = [C.c_void_p, C.POINTER(fb_params), C.c_int, c_dp, C.c_uint, C.POINTER(fb_cv_out)]
         self._eval_cv.restype = C.c_int
+        self._kernel_launches = f("kernel_launches")
+        self._kernel_launches.argtypes = [C.c_void_p]; self._kernel_launches.restype = C.c_int64
         self._gfl_solve = f("gfl_solve")
         self._gfl_solve.argtypes = [C.c_int, C.c_uint, c_dp, c_dp, C.c_double, C.c_double, C.c_int, C.c_int,
                                     C.POINTER(fb_gfl_state), c_dp]
@@ -169,6 +171,9 @@ class Handle:
         if self.h:
             self.lib._destroy(self.h)
             self.h = None
+
+    def kernel_launches(self):
+        return int(self.lib._kernel_launches(self.h))
 
     def __del__(self):
         try:

@@ -1,0 +1,89 @@
+// fb_api.cu -- the C ABI of libfastbinless_cuda.so (include/fastbinless.h). Thin: argument checks,
+// exception -> status translation, nothing else. The Rcpp shim (r/fastbinless_shim.cpp) and the ctypes
+// mirror (binless_b200/_abi.py) bind exactly these symbols.
+#include "fb_model.cuh"
+#include <string>
+
+struct fb_handle { fb::Model m; fb_handle(int nbins, const fb_mat *mat) : m(nbins, mat) {} };
+
+namespace {
+template <typename F>
+int guarded(std::string &err, F &&f) {
+    try { f(); return FB_OK; }
+    catch (const fb::ArgError &e) { err = e.what(); return FB_ERR_ARG; }
+    catch (const fb::CudaError &e) { err = e.what(); return FB_ERR_CUDA; }
+    catch (const fb::StateError &e) { err = e.what(); return FB_ERR_STATE; }
+    catch (const fb::NumError &e) { err = e.what(); return FB_ERR_NUMERIC; }
+    catch (const fb::Interrupted &e) { err = e.what(); return FB_ERR_INTERRUPT; }
+    catch (const std::bad_alloc &) { err = "out of host memory"; return FB_ERR_ARG; }
+    catch (const std::exception &e) { err = e.what(); return FB_ERR_NUMERIC; }
+}
+} // namespace
+
+extern "C" {
+
+FB_API int fb_create(int nbins, const fb_mat *mat, fb_handle **out) {
+    if (!out) { fb::g_last_error = "null handle pointer"; return FB_ERR_ARG; }
+    *out = nullptr;
+    return guarded(fb::g_last_error, [&] { *out = new fb_handle(nbins, mat); });
+}
+
+FB_API void fb_destroy(fb_handle *h) { delete h; }
+
+FB_API const char *fb_last_error(const fb_handle *h) { return h ? h->m.err.c_str() : fb::g_last_error.c_str(); }
+
+FB_API int fb_run_signal(fb_handle *h, const fb_params *p, fb_signal_out *out) {
+    if (!h) { fb::g_last_error = "null handle"; return FB_ERR_ARG; }
+    return guarded(h->m.err, [&] { h->m.run_signal(p, out); });
+}
+
+FB_API int fb_restore(fb_handle *h, const double *log_signal, const fb_mean_state *biases, const fb_gam_state *decay,
+                      const fb_mean_state *exposures) {
+    if (!h) { fb::g_last_error = "null handle"; return FB_ERR_ARG; }
+    return guarded(h->m.err, [&] { h->m.restore(log_signal, biases, decay, exposures); });
+}
+
+FB_API int fb_run_difference(fb_handle *h, int ref, const fb_params *p, fb_diff_out *out) {
+    if (!h) { fb::g_last_error = "null handle"; return FB_ERR_ARG; }
+    return guarded(h->m.err, [&] { h->m.run_difference(ref, p, out); });
+}
+
+FB_API int fb_eval_cv(fb_handle *h, const fb_params *p, int nlam, const double *lam2, unsigned group, fb_cv_out *outs) {
+    if (!h) { fb::g_last_error = "null handle"; return FB_ERR_ARG; }
+    return guarded(h->m.err, [&] { h->m.eval_cv(p, nlam, lam2, group, outs); });
+}
+
+FB_API int fb_set_interrupt_cb(fb_handle *h, int (*cb)(void *), void *arg) {
+    if (!h) return FB_ERR_ARG;
+    h->m.interrupt_cb = cb; h->m.interrupt_arg = arg;
+    return FB_OK;
+}
+
+FB_API int64_t fb_kernel_launches(const fb_handle *h) { return h ? h->m.kernel_launches : 0; }
+
+FB_API int fb_gfl_solve(int nbins, unsigned maxdiag, const double *y, const double *w, double lam2, double converge,
+                        int maxsteps, int warm, fb_gfl_state *st, double *beta_full) {
+    return guarded(fb::g_last_error, [&] {
+        int ndev = 0;
+        if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+            throw fb::CudaError("no CUDA device available (there is no CPU fallback)");
+        if (!y || !w || !st) throw fb::ArgError("null argument");
+        const size_t nc = (size_t)nbins * (nbins + 1) / 2;
+        fb::GflSolver s(nbins, maxdiag, 0);
+        s.ninner_max = maxsteps;
+        fb::DevBuf<double> dy(nc), dw(nc), dout(nc);
+        dy.upload(y, nc); dw.upload(w, nc);
+        if (warm) { s.alpha = st->alpha; s.import_state(st->beta, st->z, st->u); }
+        s.optimize(dy.p, dw.p, lam2, converge);
+        st->alpha = s.alpha; st->steps = s.last_steps;
+        s.export_state(st->beta, st->z, st->u);
+        if (beta_full) {
+            s.get_beta_full(dout.p);
+            FB_CUDA(cudaDeviceSynchronize());
+            dout.download(beta_full, nc);
+            FB_CUDA(cudaDeviceSynchronize());
+        }
+    });
+}
+
+} // extern "C"

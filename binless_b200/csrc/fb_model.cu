@@ -1,0 +1,523 @@
+// fb_model.cu -- host driver of the fast-binless path (see fb_model.cuh).
+#include "fb_model.cuh"
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <atomic>
+#include <future>
+#include <map>
+#include <thread>
+
+namespace fb {
+
+std::string g_last_error;
+
+namespace {
+
+const char *kSizeMsg = "Input size should be N(N+1)/2 dense matrix of observed counts for each dataset";
+
+// make_even_bins + bin_data with drop=true (util.cpp:56-111): bin index of each value, unused bins removed
+std::vector<int> even_bins_dropped(const std::vector<double> &v, double lower, double upper, unsigned Nbins, int &nkept) {
+    std::map<double, unsigned> edges;
+    const double size = upper - lower;
+    for (unsigned i = 0; i <= Nbins; ++i) edges[lower + i * size / double(Nbins)] = i;
+    std::vector<int> raw(v.size());
+    std::vector<char> used(Nbins, 0);
+    for (size_t k = 0; k < v.size(); ++k) {
+        auto it = edges.upper_bound(v[k]);
+        const unsigned j = (it == edges.end()) ? edges.rbegin()->second - 1 : it->second - 1;
+        raw[k] = (int)j;
+        used[j] = 1;
+    }
+    std::vector<int> remap(Nbins, -1);
+    nkept = 0;
+    for (unsigned b = 0; b < Nbins; ++b) if (used[b]) remap[b] = nkept++;
+    for (auto &r : raw) r = remap[r];
+    return raw;
+}
+
+std::vector<double> broadcast(const double *p, int np, int n) {
+    if (!p || np <= 0) return std::vector<double>(n, 0.0);
+    if (np == n) return std::vector<double>(p, p + n);
+    return std::vector<double>(n, p[0]);
+}
+
+int host_threads() {
+    unsigned h = std::thread::hardware_concurrency();
+    return (int)std::min(16u, std::max(1u, h));
+}
+
+} // namespace
+
+// ---------------------------------------------------------------------------------------------
+// ingest: FastDataCore (FastData.ipp:3-26) + verification of the bin_data layout
+// ---------------------------------------------------------------------------------------------
+Model::Model(int nbins, const fb_mat *mat) {
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+        throw CudaError("no CUDA device available (there is no CPU fallback)");
+    FB_CUDA(cudaStreamCreateWithFlags(&st_, cudaStreamNonBlocking));
+    FB_CUDA(cudaEventCreate(&ev0_));
+    FB_CUDA(cudaEventCreate(&ev1_));
+    ingest(nbins, mat);
+}
+
+Model::~Model() {
+    if (ev0_) cudaEventDestroy(ev0_);
+    if (ev1_) cudaEventDestroy(ev1_);
+    if (st_) cudaStreamDestroy(st_);
+}
+
+void Model::ingest(int nbins, const fb_mat *m) {
+    if (!m || m->N <= 0 || nbins <= 0) throw ArgError("empty input");
+    if (!m->pos1 || !m->pos2 || !m->observed || !m->nobs || !m->distance) throw ArgError("missing input column");
+    if (nbins > 65535) throw ArgError("at most 65535 bins are supported");
+    const int64_t N = m->N, n = nbins, ncells = n * (n + 1) / 2;
+    const int nthr = host_threads();
+    auto par_rows = [&](int64_t D, auto &&fn) { // fn(d, i) -> error string or nullptr, over all rows of all datasets
+        std::vector<std::future<const char *>> fut;
+        for (int tid = 0; tid < nthr; ++tid)
+            fut.push_back(std::async(std::launch::async, [&, tid]() -> const char * {
+                for (int64_t q = tid; q < D * n; q += nthr)
+                    if (const char *e = fn(q / n, q % n)) return e;
+                return nullptr;
+            }));
+        const char *err = nullptr;
+        for (auto &f : fut) { const char *e = f.get(); if (e && !err) err = e; }
+        return err;
+    };
+    int64_t D;
+    if (m->name) {
+        std::vector<std::future<std::pair<int, int>>> fut;
+        for (int tid = 0; tid < nthr; ++tid)
+            fut.push_back(std::async(std::launch::async, [&, tid]() {
+                int mn = INT32_MAX, mx = INT32_MIN;
+                const int64_t lo = N * tid / nthr, hi = N * (tid + 1) / nthr;
+                for (int64_t k = lo; k < hi; ++k) { mn = std::min(mn, m->name[k]); mx = std::max(mx, m->name[k]); }
+                return std::make_pair(mn, mx);
+            }));
+        int mn = INT32_MAX, mx = INT32_MIN;
+        for (auto &f : fut) { auto r = f.get(); mn = std::min(mn, r.first); mx = std::max(mx, r.second); }
+        D = mx;
+        if (D <= 0 || D * ncells != N) throw ArgError(kSizeMsg);
+        if (mn != 1) throw ArgError("Name column values should start at 1");
+    } else {
+        if (N % ncells != 0) throw ArgError(kSizeMsg);
+        D = N / ncells;
+    }
+    t_.n = nbins; t_.D = (int)D; t_.ncells = ncells;
+
+    // start the uploads, validate on the host meanwhile
+    obs_.alloc(N); nobs_.alloc(N);
+    auto checks = std::async(std::launch::async, [&]() -> const char * {
+        if (m->bin1 || m->bin2 || m->name) {
+            // FastData.ipp:22-25 asks for bins in [1, nbins]; this library additionally requires the
+            // (name, bin1, bin2) sort order that the reference silently relies on (fast_binless.ipp:28-30)
+            std::atomic<bool> range_bad{false};
+            const char *e = par_rows(D, [&](int64_t d, int64_t i) -> const char * {
+                const int64_t base = d * ncells + rm_start(i, n);
+                for (int64_t j = i; j < n; ++j) {
+                    const int64_t g = base + (j - i);
+                    if (m->bin1 && (m->bin1[g] < 1 || m->bin1[g] > n)) { range_bad = true; return "range"; }
+                    if (m->bin2 && (m->bin2[g] < 1 || m->bin2[g] > n)) { range_bad = true; return "range"; }
+                    if ((m->name && m->name[g] != d + 1) || (m->bin1 && m->bin1[g] != i + 1) || (m->bin2 && m->bin2[g] != j + 1))
+                        return "order";
+                }
+                return nullptr;
+            });
+            if (e) return range_bad.load() ? "bins should range from 1 to the number of bins"
+                                    : "mat must be sorted by (name, bin1, bin2) and hold every cell of the upper triangle";
+        }
+        pos_.resize(n); dist_.resize(n);
+        for (int64_t r = 0; r < n; ++r) { pos_[r] = m->pos1[rm_start(r, n)]; dist_[r] = m->distance[r]; }
+        return par_rows(D, [&](int64_t d, int64_t i) -> const char * {
+            const int64_t base = d * ncells + rm_start(i, n);
+            const double pi = pos_[i];
+            for (int64_t j = i; j < n; ++j) {
+                const int64_t g = base + (j - i);
+                if ((double)m->pos1[g] != pi || (double)m->pos2[g] != pos_[j] || m->distance[g] != dist_[j - i])
+                    return "pos1/pos2 must depend on the bin only and distance on bin2-bin1 only (bin_data layout, R/preprocess.R:104-148)";
+            }
+            return nullptr;
+        });
+    });
+    FB_CUDA(cudaMemcpyAsync(obs_.p, m->observed, N * sizeof(int32_t), cudaMemcpyHostToDevice, st_));
+    FB_CUDA(cudaMemcpyAsync(nobs_.p, m->nobs, N * sizeof(int32_t), cudaMemcpyHostToDevice, st_));
+    phi_.alloc(N); phi_new_.alloc(N); phihat_.alloc(N); wgt_.alloc(N);
+    phi_.zero(st_); phihat_.zero(st_); wgt_.zero(st_);
+    tab_.alloc(2 * (size_t)n + D); tab_old_.alloc(2 * (size_t)n + D);
+    tab_h_.alloc(2 * (size_t)n + D);
+    items_.alloc(2 * (size_t)std::max<int64_t>(n, D)); items_h_.alloc(2 * (size_t)std::max<int64_t>(n, D));
+    prec_h_.alloc(4);
+    part_.alloc(leg_part_doubles(t_));
+    scratch_.alloc(4096);
+    keys_.alloc((size_t)(2 * n + 1) * D + 8);
+    const char *e = checks.get();
+    FB_CUDA(cudaStreamSynchronize(st_));
+    if (e) throw ArgError(e);
+    for (int64_t k = 0; k < n; ++k)
+        if (!(dist_[k] > 0)) throw ArgError("distance must be positive");
+}
+
+// ---------------------------------------------------------------------------------------------
+// legs
+// ---------------------------------------------------------------------------------------------
+void Model::build_legs(double tol_val, unsigned free_decay) {
+    const int n = t_.n, D = t_.D;
+    // bias binner (fast_bias_mean.hpp:37-68): even bins between min and max position
+    {
+        const double mn = *std::min_element(pos_.begin(), pos_.end()), mx = *std::max_element(pos_.begin(), pos_.end());
+        rowbin_ = even_bins_dropped(pos_, mn, mx, (unsigned)n, nb_bias_);
+    }
+    // decay binner (fast_decay.hpp:48-68): K * bins_per_bf even bins of log(distance), empty ones dropped
+    std::vector<double> ld(n);
+    for (int k = 0; k < n; ++k) ld[k] = std::log(dist_[k]);
+    const double smin = *std::min_element(ld.begin(), ld.end()), smax = *std::max_element(ld.begin(), ld.end());
+    dbin_ = even_bins_dropped(ld, smin, smax, (unsigned)(kDecayK * kDecayBinsPerBf), nb_dec_);
+    std::vector<double> sup_num(nb_dec_, 0.0), sup_den(nb_dec_, 0.0);
+    for (int k = 0; k < n; ++k) { // mean log-distance per bin over all cells: D*(n-k) cells on diagonal k
+        const double cnt = (double)D * (double)(n - k);
+        sup_num[dbin_[k]] += cnt * ld[k]; sup_den[dbin_[k]] += cnt;
+    }
+    std::vector<double> support(nb_dec_);
+    for (int b = 0; b < nb_dec_; ++b) support[b] = sup_num[b] / sup_den[b];
+    dec_.setup(support, smin, smax, tol_val, free_decay);
+    // observables per leg bin (integers: exact in any order)
+    std::vector<double> dummy;
+    std::fill(tab_h_.p, tab_h_.p + tab_h_.n, 0.0);
+    FB_CUDA(cudaMemcpyAsync(tab_.p, tab_h_.p, tab_h_.n * sizeof(double), cudaMemcpyHostToDevice, st_));
+    leg_sums(LEG_EXPO, MODE_NOBS, expo_nobs_, dummy);
+    leg_sums(LEG_DECAY, MODE_NOBS, dec_nobs_, dummy);
+    leg_sums(LEG_BIAS, MODE_NOBS, bias_nobs_, dummy);
+    for (auto &v : bias_nobs_) v = v / 2.; // fast_bias_mean.hpp:58
+    expo_est_.assign(D, 0.0);
+    bias_est_.assign(nb_bias_, 0.0);
+    legs_built_ = true;
+}
+
+void Model::upload_tables() {
+    const int n = t_.n, D = t_.D;
+    const std::vector<double> dc = dec_.binned_estimate();
+    double *h = tab_h_.p;
+    for (int r = 0; r < n; ++r) h[r] = bias_est_[rowbin_[r]];       // Params<Mean>::mean stays 0
+    for (int k = 0; k < n; ++k) h[n + k] = dc[dbin_[k]];
+    for (int d = 0; d < D; ++d) h[2 * (size_t)n + d] = expo_est_[d];
+    FB_CUDA(cudaMemcpyAsync(tab_.p, h, tab_h_.n * sizeof(double), cudaMemcpyHostToDevice, st_));
+    FB_CUDA(cudaStreamSynchronize(st_)); // tab_h_ is reused by the next fit
+}
+
+void Model::leg_sums(int leg, int mode, std::vector<double> &a, std::vector<double> &b) {
+    leg_pass(leg, mode, t_, tables(tab_), alpha_, obs_.p, nobs_.p, phi_.p, part_.p, items_.p, st_);
+    kernel_launches += 2;
+    const int nitems = leg == LEG_EXPO ? t_.D : t_.n;
+    FB_CUDA(cudaMemcpyAsync(items_h_.p, items_.p, 2 * (size_t)nitems * sizeof(double), cudaMemcpyDeviceToHost, st_));
+    FB_CUDA(cudaStreamSynchronize(st_));
+    const int nb = leg == LEG_EXPO ? t_.D : (leg == LEG_BIAS ? nb_bias_ : nb_dec_);
+    a.assign(nb, 0.0); b.assign(nb, 0.0);
+    for (int k = 0; k < nitems; ++k) {
+        const int bin = leg == LEG_EXPO ? k : (leg == LEG_BIAS ? rowbin_[k] : dbin_[k]);
+        a[bin] += items_h_.p[2 * k]; b[bin] += items_h_.p[2 * k + 1];
+    }
+}
+
+namespace {
+// Summarizer::update_summary (fast_summarizer.ipp:32-51) / set_poisson_lsq_summary (:3-30), given the per-bin sums
+void summary_from_sums(int mode, const std::vector<double> &a, const std::vector<double> &b, const std::vector<double> &est,
+                       const std::vector<double> &nobs, std::vector<double> &phihat, std::vector<double> &weight) {
+    const size_t nb = a.size();
+    phihat.resize(nb); weight.resize(nb);
+    for (size_t k = 0; k < nb; ++k) {
+        if (mode == MODE_RESID) { // a = sum w, b = sum z*w
+            double ph = b[k] / a[k] + est[k];
+            if (a[k] == 0) ph = 0;
+            phihat[k] = ph; weight[k] = a[k];
+        } else {                  // a = sum observed, b = sum nobs*exp(log expected); pseudocount 0.01
+            double e = std::log(0.01 + a[k] / b[k]);
+            if (b[k] == 0) e = 0;
+            phihat[k] = e; weight[k] = std::exp(e) * nobs[k];
+        }
+    }
+}
+} // namespace
+
+void Model::fit_expo(int mode) {
+    std::vector<double> a, b, ph, wt;
+    leg_sums(LEG_EXPO, mode, a, b);
+    summary_from_sums(mode, a, b, expo_est_, expo_nobs_, ph, wt);
+    expo_est_ = ph; // no centring, no cap (fast_exposure.hpp:63-70)
+    upload_tables();
+}
+
+void Model::fit_bias(int mode) {
+    std::vector<double> a, b, ph, wt;
+    leg_sums(LEG_BIAS, mode, a, b);
+    summary_from_sums(mode, a, b, bias_est_, bias_nobs_, ph, wt);
+    // FitterImpl<Leg,Mean>::update_params (fast_fitter_mean.hpp:55-79): centre, then cap at 3 sd
+    double num = 0, den = 0;
+    for (int k = 0; k < nb_bias_; ++k) { num += bias_nobs_[k] * ph[k]; den += bias_nobs_[k]; }
+    const double avg = num / den;
+    for (auto &v : ph) v = v - avg;
+    double sq = 0;
+    for (double v : ph) sq += v * v;
+    const double sd = std::sqrt(sq / ph.size());
+    for (auto &v : ph) v = std::max(std::min(v, 3 * sd), -3 * sd);
+    bias_est_ = ph;
+    upload_tables();
+}
+
+void Model::fit_decay(int mode) {
+    std::vector<double> a, b, ph, wt;
+    leg_sums(LEG_DECAY, mode, a, b);
+    summary_from_sums(mode, a, b, dec_.binned_estimate(), dec_nobs_, ph, wt);
+    dec_.fit(ph, wt, dec_nobs_);
+    upload_tables();
+}
+
+void Model::check_interrupt() {
+    if (interrupt_cb && interrupt_cb(interrupt_arg)) throw Interrupted("interrupted");
+}
+
+void Model::download(double *h_dst, const double *d_src, size_t cnt) {
+    if (h_dst) FB_CUDA(cudaMemcpyAsync(h_dst, d_src, cnt * sizeof(double), cudaMemcpyDeviceToHost, st_));
+}
+
+void Model::patchnos(const double *d_value, double tol, bool compute, int32_t *h_out) {
+    if (!h_out) return;
+    const int64_t N = t_.N(), nc = t_.ncells;
+    DevBuf<int32_t> labels(N);
+    if (!compute) { fill_i32(labels.p, N, -1, st_); kernel_launches += 1; }
+    else {
+        DevBuf<int32_t> parent(nc), scan(nc + nc / 4096 + 8);
+        for (int d = 0; d < t_.D; ++d) {
+            patch_labels(t_.n, tol, d_value + (size_t)d * nc, parent.p, scan.p, labels.p + (size_t)d * nc, st_);
+            kernel_launches += 6;
+        }
+        FB_CUDA(cudaStreamSynchronize(st_));
+    }
+    FB_CUDA(cudaMemcpyAsync(h_out, labels.p, N * sizeof(int32_t), cudaMemcpyDeviceToHost, st_));
+    FB_CUDA(cudaStreamSynchronize(st_));
+}
+
+// ---------------------------------------------------------------------------------------------
+// binless() (fast_binless.cpp:85-184)
+// ---------------------------------------------------------------------------------------------
+void Model::run_signal(const fb_params *p, fb_signal_out *out) {
+    if (!p || !out) throw ArgError("null argument");
+    if (!p->lam2 || p->n_lam2 <= 0) throw ArgError("lam2 is required");
+    const int n = t_.n, D = t_.D;
+    const int64_t nc = t_.ncells, N = t_.N();
+    FB_CUDA(cudaEventRecord(ev0_, st_));
+    double ms_solver = 0;
+    kernel_launches = 0;
+    if (p->verbose) std::printf("init\n");
+    alpha_ = p->alpha;
+    const double tol_val = p->tol_val;
+    unsigned bg_steps = p->bg_steps;
+    phi_.zero(st_); phihat_.zero(st_); wgt_.zero(st_);
+    build_legs(tol_val, p->free_decay);
+    // initial Poisson fits, in this order (fast_binless.cpp:104-115)
+    fit_expo(MODE_POISSON);
+    fit_decay(MODE_POISSON);
+    fit_bias(MODE_POISSON);
+
+    double current_tol_val = 1.;
+    GflSolver flo(n, p->maxdiag, st_); // shared by all datasets: the flos copies share one strategy (GFLLibrary.hpp:59)
+    double flo_tol = current_tol_val / 20.;
+    const std::vector<double> lam2 = broadcast(p->lam2, p->n_lam2, D);
+    const std::vector<double> lam1 = broadcast(p->lam1, p->n_lam1, D);
+    int64_t n_solves = 0, iters = 0, cell_iters = 0;
+    out->nsteps = 0; out->converged = 0;
+    for (unsigned step = 1; step <= p->nouter; ++step) {
+        check_interrupt();
+        if (p->verbose) std::printf("step %u", step);
+        fit_bias(MODE_RESID);
+        const bool bg = step <= bg_steps;
+        if (bg) FB_CUDA(cudaMemcpyAsync(tab_old_.p, tab_.p, tab_.n * sizeof(double), cudaMemcpyDeviceToDevice, st_));
+        fit_decay(MODE_RESID);
+        if (bg) {
+            precision(t_, tables(tab_old_), tables(tab_), phi_.p, phi_.p, scratch_.p, scratch_.p + 8, st_);
+            kernel_launches += 3;
+        } else {
+            signal_yw(t_, tables(tab_), alpha_, obs_.p, nobs_.p, phi_.p, 0, phihat_.p, wgt_.p, st_);
+            kernel_launches += 1;
+            for (int d = 0; d < D; ++d) {
+                const int steps = flo.optimize(phihat_.p + (size_t)d * nc, wgt_.p + (size_t)d * nc, lam2[d], flo_tol);
+                ms_solver += flo.ms_last;
+                const int it = steps - 1;
+                if (out->solve_iters && n_solves < out->solve_iters_cap) out->solve_iters[n_solves] = it;
+                ++n_solves; iters += it; cell_iters += (int64_t)it * flo.grid().ncells;
+                flo.get_beta_full(phi_new_.p + (size_t)d * nc);
+                center_dataset(nc, nobs_.p + (size_t)d * nc, phi_new_.p + (size_t)d * nc, scratch_.p + 16, st_);
+                kernel_launches += 3;
+            }
+            precision(t_, tables(tab_), tables(tab_), phi_.p, phi_new_.p, scratch_.p, scratch_.p + 8, st_);
+            kernel_launches += 3;
+            std::swap(phi_.p, phi_new_.p);
+        }
+        FB_CUDA(cudaMemcpyAsync(prec_h_.p, scratch_.p + 8, 3 * sizeof(double), cudaMemcpyDeviceToHost, st_));
+        FB_CUDA(cudaStreamSynchronize(st_));
+        const double pabs = prec_h_.p[0], prel = pabs / (prec_h_.p[1] - prec_h_.p[2]);
+        if (p->verbose) std::printf(" : reached precision abs = %g rel = %g\n", pabs, prel);
+        if (step - 1 < FB_MAX_OUTER) { out->prec_abs[step - 1] = pabs; out->prec_rel[step - 1] = prel; }
+        bool converged = prel <= tol_val && current_tol_val <= tol_val * 1.01;
+        if (converged && step <= bg_steps) { converged = false; bg_steps = step; }
+        current_tol_val = std::min(current_tol_val, std::max(tol_val, pabs));
+        flo_tol = current_tol_val / 20;
+        if (converged || step == p->nouter) { shift_signal(t_, phi_.p, keys_.p, st_); kernel_launches += 3; }
+        else { remove_degeneracy(t_, phi_.p, keys_.p, st_); kernel_launches += 3; }
+        fit_expo(MODE_RESID);
+        out->nsteps = (int)step;
+        if (converged) { if (p->verbose) std::printf("converged\n"); out->converged = 1; break; }
+    }
+    kernel_launches += flo.kernel_launches;
+    if (p->verbose) std::printf("done\n");
+    FB_CUDA(cudaEventRecord(ev1_, st_));
+
+    // get_as_dataframe, Signal overload (fast_dataframe.cpp:9-110)
+    {
+        DevBuf<double> lam1_d(D), cols;
+        lam1_d.upload(lam1.data(), D, st_);
+        double *want[5] = {out->background, out->biasmat, out->decaymat, out->signal, out->binless};
+        int nwant = 0;
+        for (double *w : want) nwant += (w != nullptr);
+        double *dcol[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+        if (nwant) {
+            cols.alloc((size_t)nwant * N);
+            int k = 0;
+            for (int c = 0; c < 5; ++c) if (want[c]) dcol[c] = cols.p + (size_t)(k++) * N;
+            output_signal(t_, tables(tab_), nobs_.p, phi_.p, lam1_d.p, dcol[0], dcol[1], dcol[2], dcol[3], dcol[4], st_);
+            kernel_launches += 1;
+            for (int c = 0; c < 5; ++c) download(want[c], dcol[c], N);
+        }
+        download(out->phihat, phihat_.p, N);
+        download(out->weight, wgt_.p, N);
+        download(out->log_signal, phi_.p, N);
+        FB_CUDA(cudaStreamSynchronize(st_));
+    }
+    patchnos(phi_.p, tol_val, p->compute_patchnos != 0, out->patchno);
+    if (p->csv_out && p->csv_out[0]) throw ArgError("csv_out is not supported by the CUDA library yet");
+    // leg states (fast_binless.cpp:179-183)
+    if (out->biases.estimate) std::memcpy(out->biases.estimate, bias_est_.data(), bias_est_.size() * sizeof(double));
+    out->biases.n = nb_bias_; out->biases.mean = 0;
+    for (int k = 0; k < kDecayK; ++k) out->decay.beta[k] = dec_.beta[k];
+    out->decay.lambda = dec_.lambda; out->decay.mean = dec_.mean;
+    if (out->exposures.estimate) std::memcpy(out->exposures.estimate, expo_est_.data(), expo_est_.size() * sizeof(double));
+    out->exposures.n = D; out->exposures.mean = 0;
+    out->admm_iters = iters; out->admm_cell_iters = cell_iters; out->n_solves = n_solves;
+    float ms = 0;
+    FB_CUDA(cudaEventElapsedTime(&ms, ev0_, ev1_));
+    out->ms_total = ms; out->ms_solver = ms_solver;
+    has_state_ = true;
+}
+
+// set_state calls of fast_binless.cpp:244-260
+void Model::restore(const double *log_signal, const fb_mean_state *biases, const fb_gam_state *decay,
+                    const fb_mean_state *exposures) {
+    if (!legs_built_) build_legs(0.2, 10000);
+    if (biases) {
+        if (biases->n != nb_bias_ || !biases->estimate) throw ArgError("restored leg state has the wrong size");
+        bias_est_.assign(biases->estimate, biases->estimate + biases->n);
+        if (biases->mean != 0) for (auto &v : bias_est_) v -= biases->mean;
+    }
+    if (exposures) {
+        if (exposures->n != t_.D || !exposures->estimate) throw ArgError("restored leg state has the wrong size");
+        expo_est_.assign(exposures->estimate, exposures->estimate + exposures->n);
+        if (exposures->mean != 0) for (auto &v : expo_est_) v -= exposures->mean;
+    }
+    if (decay) {
+        dec_.beta.assign(decay->beta, decay->beta + kDecayK);
+        dec_.lambda = decay->lambda; dec_.mean = decay->mean;
+    }
+    if (log_signal) FB_CUDA(cudaMemcpyAsync(phi_.p, log_signal, t_.N() * sizeof(double), cudaMemcpyHostToDevice, st_));
+    upload_tables();
+    has_state_ = true;
+}
+
+// ---------------------------------------------------------------------------------------------
+// binless_difference (fast_binless.cpp:235-279) + step_difference (fast_binless.ipp:51-105)
+// ---------------------------------------------------------------------------------------------
+void Model::run_difference(int ref, const fb_params *p, fb_diff_out *out) {
+    if (!p || !out) throw ArgError("null argument");
+    if (!has_state_) throw StateError("run_difference needs a fitted or restored model");
+    if (!p->lam2 || p->n_lam2 <= 0) throw ArgError("lam2 is required");
+    const int n = t_.n, D = t_.D;
+    const int64_t nc = t_.ncells, N = t_.N();
+    if (p->verbose) std::printf("init\n");
+    if (D < ref || ref < 1) throw ArgError("Ref is not in the allowed range"); // FastData.hpp:90
+    alpha_ = p->alpha;
+    kernel_launches = 0;
+    FB_CUDA(cudaEventRecord(ev0_, st_));
+    const double converge = p->tol_val / 20.;
+    GflSolver flo(n, p->maxdiag, st_);
+    const std::vector<double> lam2 = broadcast(p->lam2, p->n_lam2, D - 1);
+    if (p->verbose) std::printf("compute\n");
+    DevBuf<double> phihat(N), deltahat(N), w(N), delta(N), colbuf(N);
+    diff_prepare(t_, tables(tab_), alpha_, obs_.p, nobs_.p, phi_.p, ref - 1, phihat.p, deltahat.p, w.p, st_);
+    kernel_launches += 1;
+    delta.zero(st_);
+    int64_t n_solves = 0, iters = 0, cell_iters = 0;
+    double ms_solver = 0;
+    for (int d = 0, idx = 0; d < D; ++d) {
+        if (d == ref - 1) continue;
+        const int steps = flo.optimize(deltahat.p + (size_t)d * nc, w.p + (size_t)d * nc, lam2[idx++], converge);
+        ms_solver += flo.ms_last;
+        const int it = steps - 1;
+        if (out->solve_iters && n_solves < out->solve_iters_cap) out->solve_iters[n_solves] = it;
+        ++n_solves; iters += it; cell_iters += (int64_t)it * flo.grid().ncells;
+        flo.get_beta_full(delta.p + (size_t)d * nc);
+    }
+    kernel_launches += flo.kernel_launches;
+    FB_CUDA(cudaEventRecord(ev1_, st_));
+    // Difference data frame (fast_dataframe.cpp:113-145); lam1 is not applied there
+    DevBuf<double> phi_ref;
+    if (out->phi_ref) phi_ref.alloc(N);
+    diff_finish(t_, ref - 1, phihat.p, w.p, delta.p, phi_ref.p, out->difference ? colbuf.p : nullptr, st_);
+    kernel_launches += 1;
+    download(out->difference, colbuf.p, N);
+    download(out->deltahat, deltahat.p, N);
+    download(out->weight, w.p, N);
+    download(out->phi_ref, phi_ref.p, N);
+    FB_CUDA(cudaStreamSynchronize(st_));
+    patchnos(delta.p, p->tol_val, p->compute_patchnos != 0, out->patchno);
+    if (p->verbose) std::printf("done\n");
+    out->admm_iters = iters; out->admm_cell_iters = cell_iters; out->n_solves = n_solves;
+    float ms = 0;
+    FB_CUDA(cudaEventElapsedTime(&ms, ev0_, ev1_));
+    out->ms_total = ms; out->ms_solver = ms_solver;
+}
+
+// ---------------------------------------------------------------------------------------------
+// binless_eval_cv (fast_binless.cpp:186-233)
+// ---------------------------------------------------------------------------------------------
+void Model::eval_cv(const fb_params *p, int nlam, const double *lam2v, unsigned group, fb_cv_out *outs) {
+    if (!p || !outs || !lam2v) throw ArgError("null argument");
+    if (!has_state_) throw StateError("eval_cv needs a fitted or restored model");
+    if (t_.D != 1) throw ArgError("Provide only 1 dataset!");
+    const int n = t_.n;
+    const int64_t N = t_.N();
+    alpha_ = p->alpha;
+    kernel_launches = 0;
+    const std::vector<double> lam1 = broadcast(p->lam1, p->n_lam1, 1);
+    DevBuf<double> lam1_d(1), phi_cv(N), y(N), w(N), sig(N), binl(N);
+    lam1_d.upload(lam1.data(), 1, st_);
+    GflSolver flo(n, p->maxdiag, st_); // not reset between lambdas: warm-start chain of the reference
+    for (int k = 0; k < nlam; ++k) {
+        check_interrupt();
+        signal_yw(t_, tables(tab_), alpha_, obs_.p, nobs_.p, phi_.p, group, y.p, w.p, st_);
+        flo.optimize(y.p, w.p, lam2v[k], p->tol_val / 20.);
+        flo.get_beta_full(phi_cv.p);
+        center_dataset(N, nobs_.p, phi_cv.p, scratch_.p + 16, st_);
+        fb_cv_out &o = outs[k];
+        output_signal(t_, tables(tab_), nobs_.p, phi_cv.p, lam1_d.p, nullptr, nullptr, nullptr,
+                      o.signal ? sig.p : nullptr, o.binless ? binl.p : nullptr, st_);
+        kernel_launches += 5;
+        download(o.signal, sig.p, N); download(o.binless, binl.p, N);
+        download(o.phihat, y.p, N); download(o.weight, w.p, N); download(o.log_signal, phi_cv.p, N);
+        FB_CUDA(cudaStreamSynchronize(st_));
+        patchnos(phi_cv.p, p->tol_val, true, o.patchno);
+    }
+    kernel_launches += flo.kernel_launches;
+}
+
+} // namespace fb

@@ -1,0 +1,89 @@
+// fb_model.cuh -- host driver of the fast-binless path: owns the device-resident matrix, the three
+// leg estimators and the outer IRLS loop. One Model = one fb_handle.
+//
+// Follows (paths relative to /root/reference/binless/src):
+//   binless()             fast_binless.cpp:85-184
+//   binless_eval_cv()     fast_binless.cpp:186-233
+//   binless_difference()  fast_binless.cpp:235-279
+//   step_signal / step_difference   fast_binless.ipp:2-105
+//   FastDataCore          FastData.ipp:3-26
+//   leg estimators        fast_exposure.hpp, fast_bias_mean.hpp, fast_decay.hpp, fast_fitter_mean.hpp
+#pragma once
+#include "../../include/fastbinless.h"
+#include "fb_gam.hpp"
+#include "fb_gfl.cuh"
+#include "fb_irls.cuh"
+#include <memory>
+#include <string>
+#include <vector>
+
+namespace fb {
+
+// pinned host buffer
+template <typename T>
+struct PinBuf {
+    T *p = nullptr;
+    size_t n = 0;
+    PinBuf() {}
+    PinBuf(const PinBuf &) = delete;
+    PinBuf &operator=(const PinBuf &) = delete;
+    ~PinBuf() { if (p) cudaFreeHost(p); }
+    void alloc(size_t n_) { if (p) cudaFreeHost(p); p = nullptr; n = n_; if (n) FB_CUDA(cudaMallocHost((void **)&p, n * sizeof(T))); }
+};
+
+class Model {
+public:
+    Model(int nbins, const fb_mat *mat);
+    ~Model();
+    void run_signal(const fb_params *p, fb_signal_out *out);
+    void restore(const double *log_signal, const fb_mean_state *biases, const fb_gam_state *decay,
+                 const fb_mean_state *exposures);
+    void run_difference(int ref, const fb_params *p, fb_diff_out *out);
+    void eval_cv(const fb_params *p, int nlam, const double *lam2, unsigned group, fb_cv_out *outs);
+
+    std::string err;
+    int (*interrupt_cb)(void *) = nullptr;
+    void *interrupt_arg = nullptr;
+    int64_t kernel_launches = 0;
+
+private:
+    Tri t_;
+    cudaStream_t st_ = nullptr;
+    cudaEvent_t ev0_ = nullptr, ev1_ = nullptr;
+    // device-resident matrix
+    DevBuf<int32_t> obs_, nobs_;
+    DevBuf<double> phi_, phi_new_, phihat_, wgt_;
+    // structure tables found at ingest
+    std::vector<double> pos_;   // [n] position of bin r
+    std::vector<double> dist_;  // [n] distance of diagonal k
+    // legs (host side; all O(n))
+    bool legs_built_ = false, has_state_ = false;
+    double alpha_ = 1.0;
+    int nb_bias_ = 0, nb_dec_ = 0;
+    std::vector<int> rowbin_, dbin_;                  // row -> bias bin, diagonal -> decay bin
+    std::vector<double> expo_nobs_, bias_nobs_, dec_nobs_;
+    std::vector<double> expo_est_, bias_est_;         // Params<Mean>::estimate (mean = 0)
+    DecayGam dec_;
+    // device leg tables: [brow n | ddiag n | expo D], current and the copy taken before the decay update
+    DevBuf<double> tab_, tab_old_;
+    PinBuf<double> tab_h_, items_h_, prec_h_;
+    DevBuf<double> part_, items_, scratch_;
+    DevBuf<long long> keys_;
+
+    LegTables tables(const DevBuf<double> &b) const { return LegTables{b.p, b.p + t_.n, b.p + 2 * (size_t)t_.n}; }
+    void ingest(int nbins, const fb_mat *mat);
+    void build_legs(double tol_val, unsigned free_decay);
+    void upload_tables();
+    // runs one leg pass and returns the per-bin sums (a, b) on the host
+    void leg_sums(int leg, int mode, std::vector<double> &a, std::vector<double> &b);
+    void fit_expo(int mode);
+    void fit_bias(int mode);
+    void fit_decay(int mode);
+    void check_interrupt();
+    void patchnos(const double *d_value, double tol, bool compute, int32_t *h_out);
+    void download(double *h_dst, const double *d_src, size_t n);
+};
+
+extern std::string g_last_error;
+
+} // namespace fb

@@ -176,6 +176,10 @@ FB_API int FB_NAME(gfl_solve)(int nbins, unsigned maxdiag, const double *y, cons
 
 FB_API int FB_NAME(set_interrupt_cb)(fb_handle *h, int (*cb)(void *), void *arg);
 
+/* Diagnostics: number of CUDA kernels launched by the last run_* / eval_cv call on this handle
+ * (0 for the CPU oracle, which exports the same ABI under another prefix). */
+FB_API int64_t FB_NAME(kernel_launches)(const fb_handle *h);
+
 #ifdef __cplusplus
 }
 #endif

@@ -435,11 +435,12 @@ void gi_solve(const DMat &L, const vec &g0, const DMat &CI, vec &x) {
         }
     };
 
-    for (int guard = 0; guard < 1000 * (m + 1); ++guard) {
-        /* step 1: most violated inactive constraint */
+    for (int iter = 0; iter <= 10 * m; ++iter) { /* QuadProg++.cpp:289 */
+        /* step 1: most violated inactive constraint; psi sums the inactive set only (:314-318),
+         * tolerance (m - iq) eps c1 c2 100 (:328) */
         double psi = 0;
-        for (int i = 0; i < m; ++i) { s[i] = slack(i); psi += std::min(0.0, s[i]); }
-        if (std::fabs(psi) <= m * eps * c1 * c2 * 100.0) return;
+        for (int i = 0; i < m; ++i) { s[i] = slack(i); if (!active[i]) psi += std::min(0.0, s[i]); }
+        if (std::fabs(psi) <= (m - iq) * eps * c1 * c2 * 100.0) return;
         int ip = -1; double ss = 0.0;
         for (int i = 0; i < m; ++i) if (!active[i] && s[i] < ss) { ss = s[i]; ip = i; }
         if (ip < 0) return;
@@ -474,7 +475,7 @@ void gi_solve(const DMat &L, const vec &g0, const DMat &CI, vec &x) {
             s[ip] = slack(ip);
         }
     }
-    throw NumError("quadratic program did not terminate");
+    /* iteration cap reached: the reference leaves the loop and returns the current iterate */
 }
 
 /* ------------------------------------------------------------------------
@@ -1194,6 +1195,7 @@ FB_API int fbo_run_difference(fb_handle *h, int ref, const fb_params *p, fb_diff
 FB_API int fbo_eval_cv(fb_handle *h, const fb_params *p, int nlam, const double *lam2, unsigned group, fb_cv_out *outs) {
     ORACLE_TRY(h, eval_cv(h->m, p, nlam, lam2, group, outs))
 }
+FB_API int64_t fbo_kernel_launches(const fb_handle *) { return 0; }
 FB_API int fbo_set_interrupt_cb(fb_handle *h, int (*cb)(void *), void *arg) { h->m.interrupt_cb = cb; h->m.interrupt_arg = arg; return FB_OK; }
 
 FB_API int fbo_gfl_solve(int nbins, unsigned maxdiag, const double *y, const double *w, double lam2,
