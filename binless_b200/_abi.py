@@ -187,13 +187,16 @@ class Handle:
     def __exit__(self, *a):
         self.close()
 
-    def run_signal(self, alpha, lam2, lam1=0.0, columns=True, **kw):
+    def run_signal(self, alpha, lam2, lam1=0.0, columns=True, buffers=None, **kw):
+        """``columns``: True = all data-frame columns, False = only log_signal + leg states, "none" = leg states
+        only (results stay on the device). ``buffers`` may supply preallocated (e.g. pinned) output arrays."""
         p = self.lib._params(alpha, lam2, lam1, **kw)
         N = self.N
+        buffers = buffers or {}
         names = ("background", "biasmat", "decaymat", "signal", "binless", "phihat", "weight")
-        arr = {k: np.empty(N) for k in names} if columns else {}
-        patch = np.empty(N, dtype=np.int32) if columns else None
-        log_signal = np.empty(N)
+        arr = {k: buffers.get(k, None) if buffers.get(k, None) is not None else np.empty(N) for k in names} if columns is True else {}
+        patch = (buffers.get("patchno") if buffers.get("patchno") is not None else np.empty(N, dtype=np.int32)) if columns is True else None
+        log_signal = None if columns == "none" else (buffers.get("log_signal") if buffers.get("log_signal") is not None else np.empty(N))
         b_est = np.empty(self.nbins); e_est = np.empty(self.ndatasets)
         cap = max(1, self.ndatasets * int(p.nouter))
         iters = np.zeros(cap, dtype=np.int32)
@@ -205,7 +208,7 @@ class Handle:
         rc = self.lib._run_signal(self.h, C.byref(p), C.byref(out))
         self.lib._check(rc, self.h)
         res = dict(arr)
-        if columns:
+        if columns is True:
             res["patchno"] = patch
         res.update(log_signal=log_signal,
                    biases=dict(estimate=b_est[:out.biases.n].copy(), mean=out.biases.mean),

@@ -1,0 +1,248 @@
+"""GPU (-m gpu): the CUDA library, called through the C ABI, against the CPU oracle on the same seeded inputs.
+
+Tolerances (BASELINE.json north_star): log-decay, log-biases, log-signal within 1e-6 absolute after the same
+IRLS / ADMM iteration counts; fused-patch labels bit-exact. Measured agreement is ~1e-12; the bound asserted
+here is 1e-8 so that a regression is caught long before the contractual 1e-6."""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "tools"))
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+from make_golden import CASES  # noqa: E402
+from test_golden import check_against_golden  # noqa: E402
+from binless_b200._abi import FastBinlessError, gfl_solve  # noqa: E402
+from binless_b200.synth import synth  # noqa: E402
+
+pytestmark = pytest.mark.gpu
+ATOL = 1e-8
+
+
+def maxabs(a, b):
+    return float(np.max(np.abs(np.asarray(a) - np.asarray(b)))) if np.size(a) else 0.0
+
+
+def compare_signal(og, oo):
+    dg, do = og["diagnostics"], oo["diagnostics"]
+    assert dg["nsteps"] == do["nsteps"] and dg["converged"] == do["converged"]
+    assert list(dg["solve_iters"]) == list(do["solve_iters"])          # same ADMM iteration counts
+    assert dg["admm_cell_iters"] == do["admm_cell_iters"]
+    assert maxabs(og["log_signal"], oo["log_signal"]) < ATOL          # log-signal
+    assert maxabs(og["biases"]["estimate"], oo["biases"]["estimate"]) < ATOL   # log-biases
+    assert maxabs(og["decay"]["beta"], oo["decay"]["beta"]) < ATOL
+    assert maxabs(np.log(og["decaymat"]), np.log(oo["decaymat"])) < ATOL       # log-decay per cell
+    assert maxabs(og["exposures"]["estimate"], oo["exposures"]["estimate"]) < ATOL
+    assert abs(og["decay"]["lambda_"] - oo["decay"]["lambda_"]) < 1e-7 * (1 + abs(oo["decay"]["lambda_"]))
+    assert maxabs(og["phihat"], oo["phihat"]) < 1e-7 * (1 + np.abs(oo["phihat"]).max())
+    for k in ("weight", "signal", "binless", "background", "biasmat", "decaymat"):
+        assert float(np.max(np.abs(og[k] - oo[k]) / (1 + np.abs(oo[k])))) < ATOL, k
+    assert np.array_equal(og["patchno"], oo["patchno"])                # labels bit-exact
+    assert maxabs(dg["prec_abs"], do["prec_abs"]) < ATOL
+
+
+def compare_diff(a, b):
+    assert list(a["diagnostics"]["solve_iters"]) == list(b["diagnostics"]["solve_iters"])
+    for k in ("difference", "deltahat", "weight", "phi_ref"):
+        assert float(np.max(np.abs(a[k] - b[k]) / (1 + np.abs(b[k])))) < ATOL, k
+    assert np.array_equal(a["patchno"], b["patchno"])
+
+
+SIGNAL_CASES = [
+    # n, D, seed, alpha, lam2, lam1, kwargs
+    (2, 1, 3, 0.49, 2.5, 0.0, {}),                                      # smallest grid the solver accepts
+    (3, 2, 4, 0.49, 2.5, 0.0, {}),
+    (5, 2, 3, 0.49, 2.5, 0.0, {}),
+    (33, 2, 3, 0.49, [2.53, 4.51], [0.13, 0.10], {}),                   # ragged vs the 32-wide tiles
+    (129, 1, 12, 0.7, 1.0, 0.0, {}),                                    # one past the 128-wide tile
+    (200, 2, 1, 0.49, [2.53, 4.51], [0.13, 0.10], {}),                  # config C1 (SEMA3C-like)
+    (200, 1, 1, 0.49, 2.53, 0.1, dict(tol_val=0.05, nouter=8)),         # no convergence: runs to nouter
+    (131, 3, 5, 0.6, 1.5, 0.0, dict(maxdiag=40)),                       # trapeze band
+    (64, 2, 6, 0.5, 2.5, 0.0, dict(maxdiag=33)),                        # maxdiag > (n+1)/2 falls back to triangle
+    (257, 2, 6, 0.5, 2.5, 0.0, dict(bg_steps=2, nouter=6, tol_val=0.01)),   # > 50 ADMM iterations: penalty rescale
+    (90, 2, 7, 0.5, 0.0, 0.0, {}),                                      # lam2 = 0: prox is the identity
+    (90, 2, 7, 0.5, 1e4, 0.0, dict(nouter=7)),                          # huge lam2: one constant per chain
+    (70, 2, 8, 0.5, 2.5, 0.0, dict(compute_patchnos=False)),
+    (70, 2, 8, 0.5, 2.5, 0.0, dict(bg_steps=0, nouter=3)),              # signal from the first step
+    (70, 2, 8, 0.5, 2.5, 0.0, dict(nouter=1)),
+    (150, 4, 9, 1.3, [1.0, 2.0, 3.0, 4.0], [0.0, 0.1, 0.2, 0.3], dict(free_decay=40000)),
+]
+
+
+@pytest.mark.parametrize("n,D,seed,alpha,lam2,lam1,kw", SIGNAL_CASES)
+def test_fast_binless_matches_oracle(gpu_lib, oracle, n, D, seed, alpha, lam2, lam1, kw):
+    mat = synth(n, D, 5000, seed)
+    with gpu_lib.create(mat, n) as hg, oracle.create(mat, n) as ho:
+        og = hg.run_signal(alpha, lam2, lam1, **kw)
+        oo = ho.run_signal(alpha, lam2, lam1, **kw)
+        assert hg.kernel_launches() > 0
+        compare_signal(og, oo)
+        if D > 1:
+            md = kw.get("maxdiag", 0)
+            for ref in (1, D):
+                compare_diff(hg.run_difference(ref, alpha, 3.38, 0.14, maxdiag=md),
+                             ho.run_difference(ref, alpha, 3.38, 0.14, maxdiag=md))
+        else:
+            cg = hg.eval_cv(alpha, [1.0, 5.0, 0.3], 0.05, group=1)
+            co = ho.eval_cv(alpha, [1.0, 5.0, 0.3], 0.05, group=1)
+            for a, b in zip(cg, co):
+                for k in ("signal", "binless", "phihat", "weight", "log_signal"):
+                    assert float(np.max(np.abs(a[k] - b[k]) / (1 + np.abs(b[k])))) < ATOL, k
+                assert np.array_equal(a["patchno"], b["patchno"])
+
+
+def test_sparse_and_dead_inputs(gpu_lib, oracle):
+    """Rows without observables (nobs = 0 => z = w = 0, fast_residuals.ipp:55-62) and an all-zero dataset."""
+    n = 60
+    mat = synth(n, 2, 5000, 21, depth=-5.0)          # < 1 read per cell
+    nc = n * (n + 1) // 2
+    mat["observed"][nc:] = 0                          # second dataset is empty except the corner read
+    mat["observed"][nc + n - 1] = 1
+    with gpu_lib.create(mat, n) as hg, oracle.create(mat, n) as ho:
+        compare_signal(hg.run_signal(0.5, 2.5, 0.0), ho.run_signal(0.5, 2.5, 0.0))
+
+
+@pytest.mark.parametrize("name", sorted(CASES))
+def test_cuda_reproduces_golden(gpu_lib, name):
+    check_against_golden(gpu_lib, name, exact=False)
+
+
+@pytest.mark.parametrize("n,lam,conv,maxsteps,md", [(2, 1.3, 1e-3, 30000, 0), (17, 1.3, 1e-3, 30000, 0),
+                                                      (100, 1.3, 1e-3, 30000, 0), (64, 0.0, 1e-3, 5, 0),
+                                                      (200, 2.5, 1e-12, 120, 0), (200, 2.5, 1e-12, 52, 0),
+                                                      (120, 2.0, 1e-3, 30000, 30), (300, 50.0, 1e-4, 30000, 0)])
+def test_gfl_solve_matches_oracle(gpu_lib, oracle, n, lam, conv, maxsteps, md):
+    """The stand-alone fused-lasso solve: same `step`, alpha trajectory, beta / z / u in the reference's slot order."""
+    rng = np.random.default_rng(n + maxsteps)
+    nc = n * (n + 1) // 2
+    y = rng.normal(size=nc); w = rng.uniform(0, 3, size=nc); w[rng.random(nc) < 0.2] = 0
+    a = gfl_solve(oracle, n, y, w, lam, conv, maxsteps, md)
+    b = gfl_solve(gpu_lib, n, y, w, lam, conv, maxsteps, md)
+    assert a["steps"] == b["steps"] and a["alpha"] == b["alpha"]
+    for k in ("beta", "z", "u", "beta_full"):
+        assert maxabs(a[k], b[k]) < ATOL, k
+
+
+def test_gfl_warm_start_chain(gpu_lib, oracle):
+    n = 120; nc = n * (n + 1) // 2
+    rng = np.random.default_rng(3)
+    y = rng.normal(size=nc); w = rng.uniform(0, 2, size=nc)
+    res = []
+    for lib in (gpu_lib, oracle):
+        s1 = gfl_solve(lib, n, y, w, 2.53, 1e-2)
+        s2 = gfl_solve(lib, n, y * 1.1, w, 4.0, 5e-3, state=s1)
+        res.append(s2)
+    assert res[0]["steps"] == res[1]["steps"] and res[0]["alpha"] == res[1]["alpha"]
+    assert maxabs(res[0]["beta"], res[1]["beta"]) < ATOL
+
+
+def test_restore_then_difference(gpu_lib, oracle):
+    """fast_binless_difference from a saved result (set_state path, fast_binless.cpp:244-260)."""
+    mat = synth(80, 3, 5000, 8)
+    with oracle.create(mat, 80) as ho:
+        out = ho.run_signal(0.5, 2.5, 0.0)
+        want = ho.run_difference(2, 0.5, [3.0, 1.0])
+    with gpu_lib.create(mat, 80) as hg:
+        hg.restore(out["log_signal"], out["biases"], out["decay"], out["exposures"])
+        compare_diff(hg.run_difference(2, 0.5, [3.0, 1.0]), want)
+
+
+def test_input_errors(gpu_lib):
+    """Same messages as the reference's Rcpp::stop calls (FastData.ipp:20-25, FastData.hpp:90, fast_binless.cpp:198)."""
+    mat = synth(10, 2, 5000, 1)
+    bad = dict(mat); bad["name"] = mat["name"] + 1
+    with pytest.raises(FastBinlessError, match="Input size should be"):
+        gpu_lib.create(bad, 10)
+    with pytest.raises(FastBinlessError, match="Input size should be"):
+        gpu_lib.create(mat, 11)
+    bad = dict(mat); bad["bin1"] = mat["bin1"].copy(); bad["bin1"][bad["bin1"] == 10] = 11
+    with pytest.raises(FastBinlessError, match="bins should range"):
+        gpu_lib.create(bad, 10)
+    bad = dict(mat); bad["bin2"] = mat["bin2"][::-1].copy()
+    with pytest.raises(FastBinlessError, match="sorted"):
+        gpu_lib.create(bad, 10)
+    bad = dict(mat); bad["distance"] = mat["distance"].copy(); bad["distance"][3] += 1
+    with pytest.raises(FastBinlessError, match="bin_data layout"):
+        gpu_lib.create(bad, 10)
+    with gpu_lib.create(mat, 10) as h:
+        with pytest.raises(FastBinlessError) as ei:
+            h.run_difference(1, 0.5, 2.0)
+        assert ei.value.code == 3
+        h.run_signal(0.5, 2.5)
+        with pytest.raises(FastBinlessError, match="Ref is not in the allowed range"):
+            h.run_difference(3, 0.5, 2.0)
+        with pytest.raises(FastBinlessError, match="Provide only 1 dataset"):
+            h.eval_cv(0.5, [1.0, 2.0])
+    # canonical order is implied when name / bin1 / bin2 are not passed
+    slim = {k: (None if k in ("name", "bin1", "bin2") else v) for k, v in mat.items()}
+    with gpu_lib.create(slim, 10) as h:
+        assert h.run_signal(0.5, 2.5)["diagnostics"]["nsteps"] >= 1
+
+
+def test_interrupt_callback(gpu_lib):
+    import ctypes as C
+    mat = synth(40, 1, 5000, 1)
+    CB = C.CFUNCTYPE(C.c_int, C.c_void_p)
+    calls = []
+    cb = CB(lambda arg: (calls.append(1), int(len(calls) >= 2))[1])
+    with gpu_lib.create(mat, 40) as h:
+        gpu_lib.lib.fb_set_interrupt_cb.argtypes = [C.c_void_p, CB, C.c_void_p]
+        gpu_lib.lib.fb_set_interrupt_cb(h.h, cb, None)
+        with pytest.raises(FastBinlessError) as ei:
+            h.run_signal(0.5, 2.5)
+        assert ei.value.code == 5 and len(calls) == 2
+
+
+def test_python_entry_points_mirror_r_signatures(oracle):
+    from binless_b200 import fast_binless, fast_binless_difference
+    mat = synth(64, 2, 5000, 7)
+    out = fast_binless(mat, 64, 0.49, [2.53, 4.51], [0.13, 0.10])
+    assert set(out) >= {"background", "biasmat", "decaymat", "signal", "binless", "phihat", "weight", "patchno",
+                        "biases", "decay", "exposures", "log_signal", "nbins"}
+    diff = fast_binless_difference(out, mat, 1, 0.49, 3.38, 0.14)
+    assert set(diff) >= {"difference", "deltahat", "weight", "phi_ref", "patchno"}
+    with oracle.create(mat, 64) as ho:
+        compare_signal(out, ho.run_signal(0.49, [2.53, 4.51], [0.13, 0.10]))
+        compare_diff(diff, ho.run_difference(1, 0.49, 3.38, 0.14))
+
+
+def test_full_size_c2_properties_and_determinism(gpu_lib):
+    """BASELINE config 2 (2400 bins x 4 datasets) without the oracle: size-independent properties."""
+    n, D = 2400, 4
+    mat = synth(n, D, 5000, 2)
+    nc = n * (n + 1) // 2
+    slim = {k: (None if k in ("name", "bin1", "bin2") else v) for k, v in mat.items()}
+    with gpu_lib.create(slim, n) as h:
+        a = h.run_signal(0.5, 2.5, 0.0)
+        b = h.run_signal(0.5, 2.5, 0.0)
+    for k in ("log_signal", "phihat", "weight", "binless", "patchno"):   # fixed-shape reductions: same bits every run
+        assert np.array_equal(a[k], b[k]), k
+    ls = a["log_signal"]
+    nobs = mat["nobs"].astype(np.float64)
+    for d in range(D):
+        s = slice(d * nc, (d + 1) * nc)
+        assert ls[s].min() == 0.0                                        # shift_signal
+        lab = a["patchno"][s]
+        assert lab.min() == 0 and lab[0] == 0
+        # labels are numbered in order of each component's lowest cell
+        first = np.full(lab.max() + 1, nc, dtype=np.int64)
+        np.minimum.at(first, lab, np.arange(nc))
+        assert np.all(np.diff(first) > 0)
+    assert np.allclose(a["binless"], a["decaymat"] * a["signal"], rtol=1e-12)
+    assert np.allclose(a["background"][nobs == 0], 0.0)
+    assert np.all(np.diff(a["decay"]["beta"][30:]) <= 1e-9)
+    assert a["diagnostics"]["admm_cell_iters"] == int(np.sum(a["diagnostics"]["solve_iters"])) * nc
+
+
+@pytest.mark.timeout(900)
+def test_full_size_c2_matches_oracle(gpu_lib, oracle):
+    """BASELINE config 2 against the oracle end to end (~20-30 s of single-thread CPU)."""
+    n, D = 2400, 4
+    mat = synth(n, D, 5000, 2)
+    with gpu_lib.create(mat, n) as hg:
+        og = hg.run_signal(0.5, 2.5, 0.0)
+    with oracle.create(mat, n) as ho:
+        oo = ho.run_signal(0.5, 2.5, 0.0)
+    compare_signal(og, oo)
