@@ -1,22 +1,21 @@
 // fb_gfl.cu -- ADMM kernels of the graph-fused-lasso solve (sm_100a).
 //
-// One ADMM iteration (gfl_graph_fl.c:143-183) is four launches on one stream:
-//   k_beta    closed-form beta update over 32x32 tiles of the triangle, reading the
-//             row duals in row-major and the column duals in column-major order
-//             (shared-memory tile transpose), writing beta and the two chain
-//             inputs yr = beta+u_row (row-major), yc = beta+u_col (column-major)
-//   k_chains  the 1-D fused-lasso prox of every row / column chain: one LANE per
-//             chain, 32 chains per warp, exact taut-string walk (same unique
-//             minimiser as tf_dp_weight, gfl_tf.c:184-321); emits one
-//             (position,value) marker per constant segment
-//   k_expand  warp-cooperative, fully coalesced: expands the markers to z, applies
-//             u += beta - z (gfl_graph_fl.c:306-327) and accumulates the primal /
-//             dual residual sums (gfl_graph_fl.c:329-365) as per-block partials
-//   k_ctl     single block: fixed-order reduction of the partials, convergence
-//             test, varying-penalty rule every 50 steps (gfl_graph_fl.c:163-181)
-// The host polls the control block every few iterations; once `done` is set the
-// remaining queued launches return immediately.
+// One ADMM iteration (gfl_graph_fl.c:143-183) is three launches on one stream:
+//   k_beta  closed-form beta update over 32x32 tiles of the triangle, reading the row duals in
+//           row-major and the column duals in column-major order (shared-memory tile transpose);
+//           writes beta twice: row-major (input of the row chains) and column-major (column chains)
+//   k_prox  persistent kernel, one WARP per chain (dynamic longest-first queue): stages the prefix sums
+//           of beta+u of one chain in shared memory, runs the exact 1-D fused-lasso prox as a
+//           warp-cooperative taut string (same unique minimiser as tf_dp_weight, gfl_tf.c:184-321:
+//           32 candidate end points per round, slope bounds by warp scans, first tube violation by
+//           ballot), then streams z, u += beta - z (gfl_graph_fl.c:306-327) and the residual sums
+//           (gfl_graph_fl.c:329-365) with coalesced accesses
+//   k_ctl   single block: fixed-order reduction of the per-chain partials, convergence test,
+//           varying-penalty rule every 50 steps (gfl_graph_fl.c:163-181)
+// The host polls the control block every few iterations; once `done` is set the remaining queued
+// launches return immediately.
 #include "fb_gfl.cuh"
+#include <algorithm>
 #include <cmath>
 #include <vector>
 
@@ -25,9 +24,10 @@ namespace fb {
 namespace {
 
 constexpr int TILE = 32;
-constexpr int EXPAND_WARPS = 4;
 constexpr int CTL_THREADS = 1024;
 constexpr int POLL_BATCH = 8;
+constexpr int PROX_MAX_WARPS = 16;
+constexpr unsigned FULL = 0xffffffffu;
 
 // --------------------------------------------------------------------------
 // beta update (update_beta_weight, gfl_graph_fl.c:241-264)
@@ -35,13 +35,12 @@ constexpr int POLL_BATCH = 8;
 __global__ void __launch_bounds__(TILE * 8)
 k_beta(Grid g, const GflCtl *__restrict__ ctl, const double *__restrict__ y, const double *__restrict__ w,
        const double *__restrict__ zr, double *__restrict__ ur, const double *__restrict__ zc,
-       double *__restrict__ uc, double *__restrict__ beta, double *__restrict__ yr, double *__restrict__ yc) {
+       double *__restrict__ uc, double *__restrict__ beta, double *__restrict__ betaT) {
     if (ctl->done) return;
     const int i0 = blockIdx.y * TILE, j0 = blockIdx.x * TILE;
     // tile must intersect the band 0 <= j-i < md
     if (j0 + TILE - 1 < i0 || j0 - (i0 + TILE - 1) >= g.md) return;
     __shared__ double s_tcol[TILE][TILE + 1]; // z_col - u_col, indexed [j][i]
-    __shared__ double s_ucol[TILE][TILE + 1];
     __shared__ double s_beta[TILE][TILE + 1]; // indexed [i][j]
     const int tx = threadIdx.x, ty = threadIdx.y;
     const double alpha = ctl->alpha, inflate = ctl->inflate;
@@ -50,16 +49,15 @@ k_beta(Grid g, const GflCtl *__restrict__ ctl, const double *__restrict__ y, con
     // phase A: column duals, coalesced along i in column-major storage
     for (int jj = ty; jj < TILE; jj += 8) {
         const int j = j0 + jj, i = i0 + tx;
-        double t = 0.0, u = 0.0;
+        double t = 0.0;
         if (j < g.n && i <= j && j - i < g.md && j >= 1) {
             const int64_t idx = g.cm(i, j);
-            u = uc[idx];
+            double u = uc[idx];
             if (mode == 1) { u = u / inflate; uc[idx] = u; }
             else if (mode == 2) { u = u * inflate; uc[idx] = u; }
             t = zc[idx] - u;
         }
         s_tcol[jj][tx] = t;
-        s_ucol[jj][tx] = u;
     }
     __syncthreads();
     // phase B: row duals + beta, coalesced along j in row-major storage
@@ -69,9 +67,9 @@ k_beta(Grid g, const GflCtl *__restrict__ ctl, const double *__restrict__ y, con
         if (j < g.n && i <= j && j - i < g.md) {
             const int64_t idx = g.rm(i, j);
             const bool has_row = (i <= g.n - 2), has_col = (j >= 1);
-            double r = 0.0, u = 0.0;
+            double r = 0.0;
             if (has_row) {
-                u = ur[idx];
+                double u = ur[idx];
                 if (mode == 1) { u = u / inflate; ur[idx] = u; }
                 else if (mode == 2) { u = u * inflate; ur[idx] = u; }
                 r += zr[idx] - u;
@@ -81,172 +79,160 @@ k_beta(Grid g, const GflCtl *__restrict__ ctl, const double *__restrict__ y, con
             const double wi = w[idx];
             b = (2.0 * y[idx] * wi + alpha * r) / (2.0 * wi + alpha * nz);
             beta[idx] = b;
-            if (has_row) yr[idx] = b + u;
         }
         s_beta[ii][tx] = b;
     }
     __syncthreads();
-    // phase C: column chain inputs, coalesced along i
+    // phase C: column-major copy of beta, coalesced along i
     for (int jj = ty; jj < TILE; jj += 8) {
         const int j = j0 + jj, i = i0 + tx;
-        if (j < g.n && i <= j && j - i < g.md && j >= 1) yc[g.cm(i, j)] = s_beta[tx][jj] + s_ucol[jj][tx];
+        if (j < g.n && i <= j && j - i < g.md && j >= 1) betaT[g.cm(i, j)] = s_beta[tx][jj];
     }
 }
 
 // --------------------------------------------------------------------------
-// chain prox: lane-per-chain exact taut string. For the chain y_0..y_{L-1} and
+// chain prox: one warp per chain, exact taut string. For the chain v_0..v_{L-1} (v = beta + u) and
 // tube radius lam' = lam/(alpha/2) it finds the unique minimiser of
-//   1/2 sum (x_k - y_k)^2 + lam' sum |x_{k+1} - x_k|
-// i.e. exactly what tf_dp_weight(n, y, w = alpha/2, lam) returns
-// (update_z, gfl_graph_fl.c:267-304). Slopes are kept as (numerator, length)
-// pairs and compared by cross-multiplication, so the walk has no division.
+//   1/2 sum (x_k - v_k)^2 + lam' sum |x_{k+1} - x_k|
+// i.e. exactly what tf_dp_weight(n, y = beta+u, w = alpha/2, lam) returns (update_z, gfl_graph_fl.c:267-304).
+// S[k] = sum_{i<k} (v_i - c) lives in shared memory. A segment of the solution starting at k0 from height
+// s0 = S[k0] + a (a = 0 at the chain start, +-lam' when it leaves the upper / lower tube edge) may end at k
+// with any slope in [lo_k, hi_k] = [(S[k] - lam'_k - s0)/(k-k0), (S[k] + lam'_k - s0)/(k-k0)], lam'_L = 0.
+// The string bends where lo_k exceeds the running minimum of hi (it touches the upper edge there) or hi_k
+// drops below the running maximum of lo. 32 candidates k are examined per round: running bounds by warp
+// scans, first violation by ballot. Finished segments overwrite S in place with their value c + slope.
 // --------------------------------------------------------------------------
-__global__ void __launch_bounds__(32)
-k_chains(Grid g, const GflCtl *__restrict__ ctl, const double *__restrict__ yr, const double *__restrict__ yc,
-         double *__restrict__ mr, double *__restrict__ mc, uint32_t *__restrict__ fr, uint32_t *__restrict__ fc) {
-    if (ctl->done) return;
-    const int q = blockIdx.x * 32 + threadIdx.x;
-    bool active = q < g.nchains();
-    int dir = 0, idx = 0, L = 0;
-    int64_t start = 0;
-    if (active) g.chain(q, dir, idx, L, start);
-    const double *__restrict__ Y = (dir == 0 ? yr : yc) + start;
-    double *__restrict__ M = (dir == 0 ? mr : mc) + start;
-    uint32_t *__restrict__ F = (dir == 0 ? fr : fc);
-    const double lam = ctl->lam / (ctl->alpha / 2.0);
-    const double INF = __longlong_as_double(0x7ff0000000000000LL);
-
-    if (lam == 0.0) { // tf_dp_weight copies y when lam == 0 (gfl_tf.c:210-215)
-        if (active)
-            for (int p = 0; p < L; ++p) { M[p] = Y[p]; atomicOr(&F[(start + p) >> 5], 1u << ((start + p) & 31)); }
-        return;
-    }
-
-    int k0 = 0, j = 0, kmin = 0, kmax = 0;
-    double T = 0.0, c = 0.0, a = 0.0, lenf = 0.0;
-    double nmin = -INF, dmin = 1.0, nmax = INF, dmax = 1.0;
-    double ycur = active ? Y[0] : 0.0;
-    while (__any_sync(0xffffffffu, active)) {
-        if (active) {
-            const bool last = (j + 1 == L);
-            const double ynext = last ? 0.0 : Y[j + 1]; // speculative: used unless a segment breaks
-            const double yv = ycur;
-            if (j == k0) c = yv;
-            T += yv - c;
-            lenf += 1.0;
-            const double lj = last ? 0.0 : lam;
-            const double base = T - a;
-            const double nlo = base - lj, nhi = base + lj;
-            const bool up = nlo * dmax > nmax * lenf;   // lower tube edge above the max-slope ray
-            const bool dn = nhi * dmin < nmin * lenf;   // upper tube edge below the min-slope ray
-            if (up || dn) {
-                const int kend = up ? kmax : kmin;
-                const double slope = up ? nmax / dmax : nmin / dmin;
-                M[kend - 1] = c + slope;
-                atomicOr(&F[(start + kend - 1) >> 5], 1u << ((start + kend - 1) & 31));
-                a = up ? lam : -lam;
-                k0 = kend; j = kend; kmin = kend; kmax = kend;
-                T = 0.0; lenf = 0.0;
-                nmin = -INF; dmin = 1.0; nmax = INF; dmax = 1.0;
-                ycur = Y[j];
-            } else {
-                if (nlo * dmin >= nmin * lenf) { nmin = nlo; dmin = lenf; kmin = j + 1; }
-                if (nhi * dmax <= nmax * lenf) { nmax = nhi; dmax = lenf; kmax = j + 1; }
-                if (last) {
-                    M[L - 1] = c + nlo / lenf;
-                    atomicOr(&F[(start + L - 1) >> 5], 1u << ((start + L - 1) & 31));
-                    active = false;
-                } else { ++j; ycur = ynext; }
-            }
-        }
-    }
+__device__ __forceinline__ double scan_min_incl(double v, int lane) {
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const double t = __shfl_up_sync(FULL, v, o); if (lane >= o) v = fmin(v, t); }
+    return v;
+}
+__device__ __forceinline__ double scan_max_incl(double v, int lane) {
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const double t = __shfl_up_sync(FULL, v, o); if (lane >= o) v = fmax(v, t); }
+    return v;
+}
+__device__ __forceinline__ double scan_sum_incl(double v, int lane) {
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const double t = __shfl_up_sync(FULL, v, o); if (lane >= o) v += t; }
+    return v;
 }
 
-// --------------------------------------------------------------------------
-// expand markers -> z, u update, residual partial sums. Block = EXPAND_WARPS
-// warps, each handling one 32-bit flag word (32 consecutive chain slots) of
-// chain blockIdx.y. Also clears the other parity's flag words.
-// --------------------------------------------------------------------------
-__global__ void __launch_bounds__(32 * EXPAND_WARPS)
-k_expand(Grid g, const GflCtl *__restrict__ ctl, const double *__restrict__ yr, const double *__restrict__ yc,
-         const double *__restrict__ mr, const double *__restrict__ mc, const uint32_t *__restrict__ fr,
-         const uint32_t *__restrict__ fc, uint32_t *__restrict__ fr_next, uint32_t *__restrict__ fc_next,
-         double *__restrict__ zr, double *__restrict__ ur, double *__restrict__ zc, double *__restrict__ uc,
-         double *__restrict__ partials) {
-    if (ctl->done) return;
-    __shared__ double s_p[EXPAND_WARPS], s_d[EXPAND_WARPS];
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    const int q = blockIdx.y;
-    int dir, idx, L; int64_t start;
-    g.chain(q, dir, idx, L, start);
-    const int64_t end = start + L;
-    const int64_t w_first = start >> 5, w_last = (end - 1) >> 5;
-    const int64_t wd = w_first + (int64_t)blockIdx.x * EXPAND_WARPS + wid;
-    double accp = 0.0, accd = 0.0;
-    if (wd <= w_last) {
-        const double *__restrict__ Y = dir == 0 ? yr : yc;
-        const double *__restrict__ M = dir == 0 ? mr : mc;
-        const uint32_t *__restrict__ F = dir == 0 ? fr : fc;
-        double *__restrict__ Z = dir == 0 ? zr : zc;
-        double *__restrict__ U = dir == 0 ? ur : uc;
-        const double alpha = ctl->alpha;
-        const int64_t flat = wd * 32 + lane;
-        const bool valid = flat >= start && flat < end;
-        const uint32_t own = __ballot_sync(0xffffffffu, valid);
-        const uint32_t bits = F[wd] & own;
-        const bool marked = valid && ((bits >> lane) & 1u);
-        const double mval = marked ? M[flat] : 0.0;
-        // value of the first marker beyond this word (needed by slots after the last marker here)
-        double carry = 0.0;
-        const uint32_t top = bits ? (31 - __clz(bits)) : 0;
-        const bool need_carry = (own >> 1 >> top) != 0 || bits == 0; // some valid lane above the highest marker
-        if (need_carry) {
-            int64_t ws = wd + 1;
-            for (;;) { // scan following words of this chain, 32 at a time
-                const int64_t wq = ws + lane;
-                uint32_t b = 0;
-                if (wq <= w_last) {
-                    b = F[wq];
-                    if (wq == w_last) { const int hi = (int)((end - 1) & 31); b &= (hi == 31) ? 0xffffffffu : ((2u << hi) - 1u); }
-                }
-                const uint32_t nz = __ballot_sync(0xffffffffu, b != 0);
-                if (nz) {
-                    const int src = __ffs(nz) - 1;
-                    const uint32_t bw = __shfl_sync(0xffffffffu, b, src);
-                    carry = M[(ws + src) * 32 + (__ffs(bw) - 1)];
+__device__ __forceinline__ void taut_string_warp(double *__restrict__ S, const int L, const double lam, const double c,
+                                                 const double *__restrict__ rinv, const int lane) {
+    const double INF = __longlong_as_double(0x7ff0000000000000LL);
+    int k0 = 0;
+    double s0 = 0.0;
+    while (k0 < L) {
+        double H = INF, Lw = -INF; // running min of hi / max of lo over the candidates seen so far
+        int kH = k0, kL = k0;      // where they were attained (latest on ties, as gfl_tf.c keeps the later knot)
+        int p = k0;
+        for (;;) {
+            const int k = p + 1 + lane;
+            const bool valid = k <= L;
+            double hi = INF, lo = -INF;
+            if (valid) {
+                const double base = S[k] - s0;
+                const double lamk = (k == L) ? 0.0 : lam;
+                const double ri = __ldg(rinv + (k - k0));
+                hi = (base + lamk) * ri;
+                lo = (base - lamk) * ri;
+            }
+            const double Hs = scan_min_incl(hi, lane), Ls = scan_max_incl(lo, lane);
+            double Hx = __shfl_up_sync(FULL, Hs, 1), Lx = __shfl_up_sync(FULL, Ls, 1);
+            if (lane == 0) { Hx = INF; Lx = -INF; }
+            Hx = fmin(Hx, H); Lx = fmax(Lx, Lw);
+            const bool up = valid && lo > Hx, dn = valid && hi < Lx;
+            const unsigned mask = __ballot_sync(FULL, up || dn);
+            if (mask == 0u) {
+                if (p + 32 >= L) { // candidate k = L was examined: the last segment runs to the end of the chain
+                    const double f = __shfl_sync(FULL, hi, L - p - 1);
+                    const double val = c + f;
+                    for (int i = k0 + lane; i < L; i += 32) S[i] = val;
+                    k0 = L;
                     break;
                 }
-                ws += 32; // the chain's last slot always carries a marker, so this terminates
+                const double nH = __shfl_sync(FULL, Hs, 31), nL = __shfl_sync(FULL, Ls, 31);
+                if (nH <= H) { H = nH; kH = p + 1 + (31 - __clz(__ballot_sync(FULL, hi == nH))); }
+                if (nL >= Lw) { Lw = nL; kL = p + 1 + (31 - __clz(__ballot_sync(FULL, lo == nL))); }
+                p += 32;
+                continue;
             }
-        }
-        const uint32_t higher = bits >> lane;
-        const int src = higher ? (lane + __ffs(higher) - 1) : lane;
-        double z = __shfl_sync(0xffffffffu, mval, src);
-        if (!higher) z = carry;
-        if (valid) {
-            const double yv = Y[flat], uo = U[flat], zo = Z[flat];
-            const double un = yv - z;         // u + (beta - z) with beta + u = yv
-            const double rp = (yv - uo) - z;  // beta - z
-            accp = rp * rp;
-            const double dd = alpha * (z - zo);
-            accd = dd * dd;
-            Z[flat] = z;
-            U[flat] = un;
-        }
-        if (lane == 0) { // clear the next iteration's flag word (own bits only; words are shared at chain ends)
-            uint32_t *Fn = dir == 0 ? fr_next : fc_next;
-            if (own == 0xffffffffu) Fn[wd] = 0u; else atomicAnd(&Fn[wd], ~own);
+            const int fb = __ffs(mask) - 1;
+            const bool isup = (__ballot_sync(FULL, up) >> fb) & 1u;
+            const double slope = __shfl_sync(FULL, isup ? Hx : Lx, fb);
+            const unsigned eq = __ballot_sync(FULL, isup ? (hi == slope) : (lo == slope)) & ((1u << fb) - 1u);
+            const int kend = eq ? (p + 1 + (31 - __clz(eq))) : (isup ? kH : kL);
+            const double snext = S[kend] + (isup ? lam : -lam);
+            const double val = c + slope;
+            __syncwarp();
+            for (int i = k0 + lane; i < kend; i += 32) S[i] = val;
+            __syncwarp();
+            s0 = snext;
+            k0 = kend;
+            break;
         }
     }
-    accp = warp_sum(accp); accd = warp_sum(accd);
-    if (lane == 0) { s_p[wid] = accp; s_d[wid] = accd; }
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        double p = 0.0, d = 0.0;
-        for (int k = 0; k < EXPAND_WARPS; ++k) { p += s_p[k]; d += s_d[k]; }
-        const int64_t pid = (int64_t)blockIdx.y * gridDim.x + blockIdx.x;
-        partials[2 * pid] = p;
-        partials[2 * pid + 1] = d;
+    __syncwarp();
+}
+
+__global__ void __launch_bounds__(32 * PROX_MAX_WARPS, 1)
+k_prox(Grid g, GflCtl *__restrict__ ctl, const double *__restrict__ beta, const double *__restrict__ betaT,
+       double *__restrict__ zr, double *__restrict__ ur, double *__restrict__ zc, double *__restrict__ uc,
+       const double *__restrict__ rinv, double *__restrict__ partials, int stride) {
+    if (ctl->done) return;
+    extern __shared__ double smem[];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    double *__restrict__ S = smem + (size_t)wid * stride;
+    const double alpha = ctl->alpha;
+    const double lam = ctl->lam / (alpha / 2.0);
+    const int nchains = g.nchains();
+    for (;;) {
+        int q = 0;
+        if (lane == 0) q = atomicAdd(&ctl->next_chain, 1);
+        q = __shfl_sync(FULL, q, 0);
+        if (q >= nchains) break;
+        int dir, idx, L; int64_t start;
+        g.chain(q, dir, idx, L, start);
+        const double *__restrict__ B = (dir == 0 ? beta : betaT) + start;
+        double *__restrict__ Z = (dir == 0 ? zr : zc) + start;
+        double *__restrict__ U = (dir == 0 ? ur : uc) + start;
+        if (lam == 0.0 || L == 1) { // tf_dp_weight copies y (gfl_tf.c:210-215)
+            for (int k = lane; k < L; k += 32) S[k] = B[k] + U[k];
+        } else {
+            const double c = B[0] + U[0];
+            double carry = 0.0;
+            if (lane == 0) S[0] = 0.0;
+            for (int p = 0; p < L; p += 128) {
+                double v[4];
+#pragma unroll
+                for (int b = 0; b < 4; ++b) { const int k = p + 32 * b + lane; v[b] = k < L ? (B[k] + U[k]) - c : 0.0; }
+#pragma unroll
+                for (int b = 0; b < 4; ++b) {
+                    const int k = p + 32 * b + lane;
+                    const double x = scan_sum_incl(v[b], lane) + carry;
+                    if (k < L) S[k + 1] = x;
+                    carry = __shfl_sync(FULL, x, 31);
+                }
+            }
+            __syncwarp();
+            taut_string_warp(S, L, lam, c, rinv, lane);
+        }
+        __syncwarp();
+        // u += beta - z, residual sums (gfl_graph_fl.c:306-365)
+        double ap = 0.0, ad = 0.0;
+        for (int k = lane; k < L; k += 32) {
+            const double z = S[k], b = B[k], uo = U[k], zo = Z[k];
+            const double r = b - z;
+            U[k] = uo + r;
+            Z[k] = z;
+            ap += r * r;
+            const double dd = alpha * (z - zo);
+            ad += dd * dd;
+        }
+        ap = warp_sum(ap); ad = warp_sum(ad);
+        if (lane == 0) { partials[2 * q] = ap; partials[2 * q + 1] = ad; }
+        __syncwarp();
     }
 }
 
@@ -277,6 +263,7 @@ k_ctl(GflCtl *ctl, const double *__restrict__ partials, int npart, int64_t ncell
         ctl->rescale = rescale;
         ++step;
         ctl->step = step;
+        ctl->next_chain = 0; // work queue of the next k_prox launch
         ctl->done = !(step < ctl->maxsteps && cur > ctl->converge);
     }
 }
@@ -340,15 +327,29 @@ GflSolver::GflSolver(int nbins, unsigned maxdiag, cudaStream_t stream) : nbins_(
     if (nbins < 2) throw ArgError("fused lasso needs at least 2 bins");
     g_ = Grid::make(nbins, (int)md);
     const int64_t N = g_.ncells;
-    beta_.alloc(N); yr_.alloc(N); yc_.alloc(N); zr_.alloc(N); ur_.alloc(N); zc_.alloc(N); uc_.alloc(N);
-    mr_.alloc(N); mc_.alloc(N);
-    nwords_ = (N + 31) / 32 + 1;
-    flags_.alloc(4 * nwords_);
+    beta_.alloc(N); betaT_.alloc(N); zr_.alloc(N); ur_.alloc(N); zc_.alloc(N); uc_.alloc(N);
     if (trapeze_) { yband_.alloc(N); wband_.alloc(N); fillavg_.alloc(1); }
-    const int maxwords = (g_.row_len(0) + 31) / 32 + 1;
-    const int gx = (maxwords + EXPAND_WARPS - 1) / EXPAND_WARPS;
-    n_partials_ = gx * g_.nchains();
+    n_partials_ = g_.nchains();
     partials_.alloc(2 * (size_t)std::max(n_partials_, nbins));
+    // k_prox: one warp per chain, the chain's prefix sums in shared memory (8 (Lmax + 1) bytes per warp)
+    {
+        int dev = 0, smem_max = 0;
+        FB_CUDA(cudaGetDevice(&dev));
+        FB_CUDA(cudaDeviceGetAttribute(&smem_max, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+        FB_CUDA(cudaDeviceGetAttribute(&n_sm_, cudaDevAttrMultiProcessorCount, dev));
+        const int lmax = g_.row_len(0);
+        prox_stride_ = (lmax + 2) & ~1;
+        prox_warps_ = std::min<int64_t>(PROX_MAX_WARPS, (int64_t)smem_max / ((int64_t)prox_stride_ * 8));
+        if (prox_warps_ < 1) throw ArgError("chains longer than 29000 cells are not supported by this build of the fused-lasso prox");
+        prox_warps_ = std::min(prox_warps_, std::max(1, (g_.nchains() + n_sm_ - 1) / n_sm_));
+        prox_smem_ = (size_t)prox_warps_ * prox_stride_ * 8;
+        FB_CUDA(cudaFuncSetAttribute(k_prox, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)prox_smem_));
+        prox_grid_ = std::min(n_sm_, (g_.nchains() + prox_warps_ - 1) / prox_warps_);
+        std::vector<double> ri(lmax + 1, 0.0);
+        for (int m = 1; m <= lmax; ++m) ri[m] = 1.0 / (double)m;
+        rinv_.alloc(lmax + 1);
+        FB_CUDA(cudaMemcpy(rinv_.p, ri.data(), ri.size() * sizeof(double), cudaMemcpyHostToDevice));
+    }
     ctl_.alloc(1);
     FB_CUDA(cudaMallocHost((void **)&h_ctl_, sizeof(GflCtl)));
     FB_CUDA(cudaEventCreate(&ev0_)); FB_CUDA(cudaEventCreate(&ev1_));
@@ -364,21 +365,17 @@ void GflSolver::reset() {
     counter = 0;
     alpha = 5.0;
     beta_.zero(st_); zr_.zero(st_); ur_.zero(st_); zc_.zero(st_); uc_.zero(st_);
-    yr_.zero(st_); yc_.zero(st_); mr_.zero(st_); mc_.zero(st_);
+    betaT_.zero(st_);
 }
 
 void GflSolver::iteration(const double *y, const double *w, int parity) {
-    uint32_t *f_cur = flags_.p + (size_t)parity * 2 * nwords_;
-    uint32_t *f_nxt = flags_.p + (size_t)(parity ^ 1) * 2 * nwords_;
+    (void)parity;
     dim3 tb(TILE, 8), tg((g_.n + TILE - 1) / TILE, (g_.n + TILE - 1) / TILE);
-    k_beta<<<tg, tb, 0, st_>>>(g_, ctl_.p, y, w, zr_.p, ur_.p, zc_.p, uc_.p, beta_.p, yr_.p, yc_.p);
-    k_chains<<<(g_.nchains() + 31) / 32, 32, 0, st_>>>(g_, ctl_.p, yr_.p, yc_.p, mr_.p, mc_.p, f_cur, f_cur + nwords_);
-    const int maxwords = (g_.row_len(0) + 31) / 32 + 1;
-    dim3 eg((maxwords + EXPAND_WARPS - 1) / EXPAND_WARPS, g_.nchains());
-    k_expand<<<eg, 32 * EXPAND_WARPS, 0, st_>>>(g_, ctl_.p, yr_.p, yc_.p, mr_.p, mc_.p, f_cur, f_cur + nwords_,
-                                               f_nxt, f_nxt + nwords_, zr_.p, ur_.p, zc_.p, uc_.p, partials_.p);
+    k_beta<<<tg, tb, 0, st_>>>(g_, ctl_.p, y, w, zr_.p, ur_.p, zc_.p, uc_.p, beta_.p, betaT_.p);
+    k_prox<<<prox_grid_, 32 * prox_warps_, prox_smem_, st_>>>(g_, ctl_.p, beta_.p, betaT_.p, zr_.p, ur_.p, zc_.p, uc_.p,
+                                                             rinv_.p, partials_.p, prox_stride_);
     k_ctl<<<1, CTL_THREADS, 0, st_>>>(ctl_.p, partials_.p, n_partials_, g_.ncells, 2 * g_.ncells - 2);
-    kernel_launches += 4;
+    kernel_launches += 3;
 }
 
 int GflSolver::optimize(const double *d_y_tri, const double *d_w_tri, double lam2, double converge) {
@@ -396,10 +393,9 @@ int GflSolver::optimize(const double *d_y_tri, const double *d_w_tri, double lam
     c.alpha = alpha; c.lam = lam2; c.converge = converge; c.inflate = inflate;
     c.presnorm = c.dresnorm = 0; c.step = 1; c.maxsteps = ninner_max;
     c.done = !(c.step < c.maxsteps && (converge + 1) > converge);
-    c.rescale = 0;
+    c.rescale = 0; c.next_chain = 0;
     *h_ctl_ = c;
     FB_CUDA(cudaMemcpyAsync(ctl_.p, h_ctl_, sizeof(GflCtl), cudaMemcpyHostToDevice, st_));
-    flags_.zero(st_);
     int parity = 0;
     bool done = c.done != 0;
     while (!done) {

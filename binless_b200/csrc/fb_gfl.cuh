@@ -53,6 +53,7 @@ struct GflCtl {
     double presnorm, dresnorm;
     int step, maxsteps, done;
     int rescale;      // pending dual rescale: 0 none, 1 u /= inflate, 2 u *= inflate
+    int next_chain;   // work queue head of k_prox (longest chains first)
 };
 
 // One GFLLibrary strategy object: persistent beta / z / u / alpha (warm start)
@@ -88,14 +89,14 @@ private:
     int nbins_;
     bool trapeze_;
     cudaStream_t st_;
-    DevBuf<double> beta_, yr_, yc_, zr_, ur_, zc_, uc_, mr_, mc_, yband_, wband_, fillavg_;
-    DevBuf<uint32_t> flags_;           // [2 parities][2 directions][nwords]
+    DevBuf<double> beta_, betaT_, zr_, ur_, zc_, uc_, yband_, wband_, fillavg_, rinv_;
     DevBuf<double> partials_;
     DevBuf<GflCtl> ctl_;
     GflCtl *h_ctl_ = nullptr;          // pinned
     const double *y_tri_ = nullptr, *w_tri_ = nullptr;
-    int64_t nwords_ = 0;
     int n_partials_ = 0;
+    int n_sm_ = 148, prox_warps_ = 1, prox_grid_ = 1, prox_stride_ = 0;
+    size_t prox_smem_ = 0;
     cudaEvent_t ev0_, ev1_;
     void iteration(const double *y, const double *w, int parity);
 };
