@@ -118,51 +118,108 @@ __device__ __forceinline__ double scan_sum_incl(double v, int lane) {
     return v;
 }
 
+// One round examines 32*PB consecutive candidates, lane l owning the PB consecutive ones starting at
+// p + 1 + l*PB (PB odd: conflict-free 8-byte shared-memory accesses). Violations against the lane-local running
+// bounds are found before the warp scan, those against earlier lanes / earlier rounds after it with PB
+// independent compares.
+constexpr int PB = 7;
+constexpr int PW = 32 * PB;
+
+// latest b (< limit) with x[b] == v, or -1
+__device__ __forceinline__ int latest_equal(const double (&x)[PB], double v, int limit) {
+    int r = -1;
+#pragma unroll
+    for (int b = 0; b < PB; ++b) if (b < limit && x[b] == v) r = b;
+    return r;
+}
+
 __device__ __forceinline__ void taut_string_warp(double *__restrict__ S, const int L, const double lam, const double c,
-                                                 const double *__restrict__ rinv, const int lane) {
+                                                 const double *__restrict__ R, const int lane) {
     const double INF = __longlong_as_double(0x7ff0000000000000LL);
     int k0 = 0;
     double s0 = 0.0;
     while (k0 < L) {
-        double H = INF, Lw = -INF; // running min of hi / max of lo over the candidates seen so far
+        double H = INF, Lw = -INF; // running min of hi / max of lo over the rounds already examined
         int kH = k0, kL = k0;      // where they were attained (latest on ties, as gfl_tf.c keeps the later knot)
         int p = k0;
         for (;;) {
-            const int k = p + 1 + lane;
-            const bool valid = k <= L;
-            double hi = INF, lo = -INF;
-            if (valid) {
-                const double base = S[k] - s0;
-                const double lamk = (k == L) ? 0.0 : lam;
-                const double ri = __ldg(rinv + (k - k0));
-                hi = (base + lamk) * ri;
-                lo = (base - lamk) * ri;
+            const int kb = p + 1 + lane * PB;
+            double hi[PB], lo[PB];
+            double hmin = INF, lmax = -INF;
+            unsigned upm = 0, dnm = 0;
+#pragma unroll
+            for (int b = 0; b < PB; ++b) {
+                const int k = kb + b;
+                double h = INF, l = -INF;
+                if (k <= L) {
+                    const double base = S[k] - s0;
+                    const double lamk = (k == L) ? 0.0 : lam;
+                    const double ri = R[k - k0];
+                    h = (base + lamk) * ri;
+                    l = (base - lamk) * ri;
+                }
+                hi[b] = h; lo[b] = l;
+                if (l > hmin) upm |= 1u << b;
+                if (h < lmax) dnm |= 1u << b;
+                hmin = fmin(hmin, h); lmax = fmax(lmax, l);
             }
-            const double Hs = scan_min_incl(hi, lane), Ls = scan_max_incl(lo, lane);
+            const double Hs = scan_min_incl(hmin, lane), Ls = scan_max_incl(lmax, lane);
             double Hx = __shfl_up_sync(FULL, Hs, 1), Lx = __shfl_up_sync(FULL, Ls, 1);
             if (lane == 0) { Hx = INF; Lx = -INF; }
             Hx = fmin(Hx, H); Lx = fmax(Lx, Lw);
-            const bool up = valid && lo > Hx, dn = valid && hi < Lx;
-            const unsigned mask = __ballot_sync(FULL, up || dn);
+#pragma unroll
+            for (int b = 0; b < PB; ++b) {
+                if (lo[b] > Hx) upm |= 1u << b;
+                if (hi[b] < Lx) dnm |= 1u << b;
+            }
+            const unsigned anym = upm | dnm;
+            const unsigned mask = __ballot_sync(FULL, anym != 0u);
             if (mask == 0u) {
-                if (p + 32 >= L) { // candidate k = L was examined: the last segment runs to the end of the chain
-                    const double f = __shfl_sync(FULL, hi, L - p - 1);
-                    const double val = c + f;
+                if (p + PW >= L) { // candidate k = L was examined: the last segment runs to the end of the chain
+                    const double val = c + ((S[L] - s0) + 0.0) * R[L - k0];
+                    __syncwarp();
                     for (int i = k0 + lane; i < L; i += 32) S[i] = val;
                     k0 = L;
                     break;
                 }
                 const double nH = __shfl_sync(FULL, Hs, 31), nL = __shfl_sync(FULL, Ls, 31);
-                if (nH <= H) { H = nH; kH = p + 1 + (31 - __clz(__ballot_sync(FULL, hi == nH))); }
-                if (nL >= Lw) { Lw = nL; kL = p + 1 + (31 - __clz(__ballot_sync(FULL, lo == nL))); }
-                p += 32;
+                if (nH <= H) {
+                    H = nH;
+                    const int src = 31 - __clz(__ballot_sync(FULL, hmin == nH));
+                    kH = __shfl_sync(FULL, kb + latest_equal(hi, nH, PB), src);
+                }
+                if (nL >= Lw) {
+                    Lw = nL;
+                    const int src = 31 - __clz(__ballot_sync(FULL, lmax == nL));
+                    kL = __shfl_sync(FULL, kb + latest_equal(lo, nL, PB), src);
+                }
+                p += PW;
                 continue;
             }
             const int fb = __ffs(mask) - 1;
-            const bool isup = (__ballot_sync(FULL, up) >> fb) & 1u;
-            const double slope = __shfl_sync(FULL, isup ? Hx : Lx, fb);
-            const unsigned eq = __ballot_sync(FULL, isup ? (hi == slope) : (lo == slope)) & ((1u << fb) - 1u);
-            const int kend = eq ? (p + 1 + (31 - __clz(eq))) : (isup ? kH : kL);
+            // lane fb: first violating candidate, the bound it violates and where that bound was attained
+            int isup = 0, kend = -1;
+            double slope = 0.0;
+            if (lane == fb) {
+                const int bv = __ffs(anym) - 1;
+                isup = (upm >> bv) & 1u;
+                double pm = isup ? INF : -INF;
+#pragma unroll
+                for (int b = 0; b < PB; ++b)
+                    if (b < bv) pm = isup ? fmin(pm, hi[b]) : fmax(pm, lo[b]);
+                if (isup) { slope = fmin(Hx, pm); if (pm <= Hx) kend = kb + latest_equal(hi, slope, bv); }
+                else      { slope = fmax(Lx, pm); if (pm >= Lx) kend = kb + latest_equal(lo, slope, bv); }
+            }
+            isup = __shfl_sync(FULL, isup, fb);
+            slope = __shfl_sync(FULL, slope, fb);
+            kend = __shfl_sync(FULL, kend, fb);
+            if (kend < 0) { // attained in an earlier lane of this round, else in an earlier round
+                const unsigned eq = __ballot_sync(FULL, lane < fb && (isup ? hmin : lmax) == slope);
+                if (eq) {
+                    const int src = 31 - __clz(eq);
+                    kend = __shfl_sync(FULL, kb + (isup ? latest_equal(hi, slope, PB) : latest_equal(lo, slope, PB)), src);
+                } else kend = isup ? kH : kL;
+            }
             const double snext = S[kend] + (isup ? lam : -lam);
             const double val = c + slope;
             __syncwarp();
@@ -179,60 +236,88 @@ __device__ __forceinline__ void taut_string_warp(double *__restrict__ S, const i
 __global__ void __launch_bounds__(32 * PROX_MAX_WARPS, 1)
 k_prox(Grid g, GflCtl *__restrict__ ctl, const double *__restrict__ beta, const double *__restrict__ betaT,
        double *__restrict__ zr, double *__restrict__ ur, double *__restrict__ zc, double *__restrict__ uc,
-       const double *__restrict__ rinv, double *__restrict__ partials, int stride) {
+       double *__restrict__ partials, int stride, int rlen) {
     if (ctl->done) return;
     extern __shared__ double smem[];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    double *__restrict__ S = smem + (size_t)wid * stride;
+    double *__restrict__ R = smem;                                   // R[m] = 1/m, m = 1..rlen-1
+    double *__restrict__ S = smem + rlen + (size_t)wid * stride;
+    for (int m = threadIdx.x; m < rlen; m += blockDim.x) R[m] = m ? 1.0 / (double)m : 0.0;
+    __syncthreads();
     const double alpha = ctl->alpha;
     const double lam = ctl->lam / (alpha / 2.0);
     const int nchains = g.nchains();
-    for (;;) {
-        int q = 0;
-        if (lane == 0) q = atomicAdd(&ctl->next_chain, 1);
-        q = __shfl_sync(FULL, q, 0);
-        if (q >= nchains) break;
+    int q = 0;
+    if (lane == 0) q = atomicAdd(&ctl->next_chain, 1);
+    q = __shfl_sync(FULL, q, 0);
+    while (q < nchains) {
+        int qnext = 0;
+        if (lane == 0) qnext = atomicAdd(&ctl->next_chain, 1); // consumed after this chain: latency hidden
         int dir, idx, L; int64_t start;
         g.chain(q, dir, idx, L, start);
         const double *__restrict__ B = (dir == 0 ? beta : betaT) + start;
         double *__restrict__ Z = (dir == 0 ? zr : zc) + start;
         double *__restrict__ U = (dir == 0 ? ur : uc) + start;
+        // stage v = beta + u at S[k+1], coalesced, 8 loads per array in flight
+        for (int p = 0; p < L; p += 256) {
+            double vb[8], vu[8];
+#pragma unroll
+            for (int b = 0; b < 8; ++b) { const int k = p + 32 * b + lane; vb[b] = k < L ? B[k] : 0.0; vu[b] = k < L ? U[k] : 0.0; }
+#pragma unroll
+            for (int b = 0; b < 8; ++b) { const int k = p + 32 * b + lane; if (k < L) S[k + 1] = vb[b] + vu[b]; }
+        }
+        __syncwarp();
+        int so = 0; // solution at S[k + so]
         if (lam == 0.0 || L == 1) { // tf_dp_weight copies y (gfl_tf.c:210-215)
-            for (int k = lane; k < L; k += 32) S[k] = B[k] + U[k];
+            so = 1;
         } else {
-            const double c = B[0] + U[0];
+            // in-place prefix sums S[k+1] = sum_{i<=k} (v_i - c): lane-local runs of PB, one warp scan per 32*PB
+            const double c = S[1];
             double carry = 0.0;
-            if (lane == 0) S[0] = 0.0;
-            for (int p = 0; p < L; p += 128) {
-                double v[4];
+            for (int p = 0; p < L; p += PW) {
+                const int kb = p + lane * PB;
+                double t[PB];
+                double run = 0.0;
 #pragma unroll
-                for (int b = 0; b < 4; ++b) { const int k = p + 32 * b + lane; v[b] = k < L ? (B[k] + U[k]) - c : 0.0; }
+                for (int b = 0; b < PB; ++b) { const int k = kb + b; run += (k < L) ? S[k + 1] - c : 0.0; t[b] = run; }
+                const double incl = scan_sum_incl(run, lane);
+                const double off = (incl - run) + carry;
 #pragma unroll
-                for (int b = 0; b < 4; ++b) {
-                    const int k = p + 32 * b + lane;
-                    const double x = scan_sum_incl(v[b], lane) + carry;
-                    if (k < L) S[k + 1] = x;
-                    carry = __shfl_sync(FULL, x, 31);
-                }
+                for (int b = 0; b < PB; ++b) { const int k = kb + b; if (k < L) S[k + 1] = t[b] + off; }
+                carry += __shfl_sync(FULL, incl, 31);
             }
+            if (lane == 0) S[0] = 0.0;
             __syncwarp();
-            taut_string_warp(S, L, lam, c, rinv, lane);
+            taut_string_warp(S, L, lam, c, R, lane);
         }
         __syncwarp();
         // u += beta - z, residual sums (gfl_graph_fl.c:306-365)
         double ap = 0.0, ad = 0.0;
-        for (int k = lane; k < L; k += 32) {
-            const double z = S[k], b = B[k], uo = U[k], zo = Z[k];
-            const double r = b - z;
-            U[k] = uo + r;
-            Z[k] = z;
-            ap += r * r;
-            const double dd = alpha * (z - zo);
-            ad += dd * dd;
+        for (int p = 0; p < L; p += 128) {
+            double b4[4], u4[4], z4[4];
+#pragma unroll
+            for (int b = 0; b < 4; ++b) {
+                const int k = p + 32 * b + lane;
+                b4[b] = k < L ? B[k] : 0.0; u4[b] = k < L ? U[k] : 0.0; z4[b] = k < L ? Z[k] : 0.0;
+            }
+#pragma unroll
+            for (int b = 0; b < 4; ++b) {
+                const int k = p + 32 * b + lane;
+                if (k < L) {
+                    const double z = S[k + so];
+                    const double r = b4[b] - z;
+                    U[k] = u4[b] + r;
+                    Z[k] = z;
+                    ap += r * r;
+                    const double dd = alpha * (z - z4[b]);
+                    ad += dd * dd;
+                }
+            }
         }
         ap = warp_sum(ap); ad = warp_sum(ad);
         if (lane == 0) { partials[2 * q] = ap; partials[2 * q + 1] = ad; }
         __syncwarp();
+        q = __shfl_sync(FULL, qnext, 0);
     }
 }
 
@@ -338,17 +423,14 @@ GflSolver::GflSolver(int nbins, unsigned maxdiag, cudaStream_t stream) : nbins_(
         FB_CUDA(cudaDeviceGetAttribute(&smem_max, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
         FB_CUDA(cudaDeviceGetAttribute(&n_sm_, cudaDevAttrMultiProcessorCount, dev));
         const int lmax = g_.row_len(0);
-        prox_stride_ = (lmax + 2) & ~1;
-        prox_warps_ = std::min<int64_t>(PROX_MAX_WARPS, (int64_t)smem_max / ((int64_t)prox_stride_ * 8));
-        if (prox_warps_ < 1) throw ArgError("chains longer than 29000 cells are not supported by this build of the fused-lasso prox");
+        prox_stride_ = lmax + 2;
+        prox_rlen_ = lmax + 1;
+        prox_warps_ = std::min<int64_t>(PROX_MAX_WARPS, ((int64_t)smem_max / 8 - prox_rlen_) / (int64_t)prox_stride_);
+        if (prox_warps_ < 1) throw ArgError("chains longer than 14500 cells are not supported by this build of the fused-lasso prox");
         prox_warps_ = std::min(prox_warps_, std::max(1, (g_.nchains() + n_sm_ - 1) / n_sm_));
-        prox_smem_ = (size_t)prox_warps_ * prox_stride_ * 8;
+        prox_smem_ = ((size_t)prox_warps_ * prox_stride_ + prox_rlen_) * 8;
         FB_CUDA(cudaFuncSetAttribute(k_prox, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)prox_smem_));
         prox_grid_ = std::min(n_sm_, (g_.nchains() + prox_warps_ - 1) / prox_warps_);
-        std::vector<double> ri(lmax + 1, 0.0);
-        for (int m = 1; m <= lmax; ++m) ri[m] = 1.0 / (double)m;
-        rinv_.alloc(lmax + 1);
-        FB_CUDA(cudaMemcpy(rinv_.p, ri.data(), ri.size() * sizeof(double), cudaMemcpyHostToDevice));
     }
     ctl_.alloc(1);
     FB_CUDA(cudaMallocHost((void **)&h_ctl_, sizeof(GflCtl)));
@@ -373,7 +455,7 @@ void GflSolver::iteration(const double *y, const double *w, int parity) {
     dim3 tb(TILE, 8), tg((g_.n + TILE - 1) / TILE, (g_.n + TILE - 1) / TILE);
     k_beta<<<tg, tb, 0, st_>>>(g_, ctl_.p, y, w, zr_.p, ur_.p, zc_.p, uc_.p, beta_.p, betaT_.p);
     k_prox<<<prox_grid_, 32 * prox_warps_, prox_smem_, st_>>>(g_, ctl_.p, beta_.p, betaT_.p, zr_.p, ur_.p, zc_.p, uc_.p,
-                                                             rinv_.p, partials_.p, prox_stride_);
+                                                             partials_.p, prox_stride_, prox_rlen_);
     k_ctl<<<1, CTL_THREADS, 0, st_>>>(ctl_.p, partials_.p, n_partials_, g_.ncells, 2 * g_.ncells - 2);
     kernel_launches += 3;
 }

@@ -89,13 +89,13 @@ private:
     int nbins_;
     bool trapeze_;
     cudaStream_t st_;
-    DevBuf<double> beta_, betaT_, zr_, ur_, zc_, uc_, yband_, wband_, fillavg_, rinv_;
+    DevBuf<double> beta_, betaT_, zr_, ur_, zc_, uc_, yband_, wband_, fillavg_;
     DevBuf<double> partials_;
     DevBuf<GflCtl> ctl_;
     GflCtl *h_ctl_ = nullptr;          // pinned
     const double *y_tri_ = nullptr, *w_tri_ = nullptr;
     int n_partials_ = 0;
-    int n_sm_ = 148, prox_warps_ = 1, prox_grid_ = 1, prox_stride_ = 0;
+    int n_sm_ = 148, prox_warps_ = 1, prox_grid_ = 1, prox_stride_ = 0, prox_rlen_ = 0;
     size_t prox_smem_ = 0;
     cudaEvent_t ev0_, ev1_;
     void iteration(const double *y, const double *w, int parity);
