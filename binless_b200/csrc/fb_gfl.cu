@@ -27,6 +27,7 @@ constexpr int TILE = 32;
 constexpr int CTL_THREADS = 1024;
 constexpr int POLL_BATCH = 8;
 constexpr int PROX_MAX_WARPS = 16;
+constexpr int PB = 7, PW = 32 * PB;   // run length of the blocked prefix-sum pass
 constexpr unsigned FULL = 0xffffffffu;
 
 // --------------------------------------------------------------------------
@@ -118,19 +119,123 @@ __device__ __forceinline__ double scan_sum_incl(double v, int lane) {
     return v;
 }
 
-// One round examines 32*PB consecutive candidates, lane l owning the PB consecutive ones starting at
-// p + 1 + l*PB (PB odd: conflict-free 8-byte shared-memory accesses). Violations against the lane-local running
-// bounds are found before the warp scan, those against earlier lanes / earlier rounds after it with PB
-// independent compares.
-constexpr int PB = 7;
-constexpr int PW = 32 * PB;
+// One round examines 32*B consecutive candidates, lane l owning the B consecutive ones starting at
+// p + 1 + l*B (B odd: conflict-free 8-byte shared-memory accesses). Violations against the lane-local running
+// bounds are found before the warp scan, those against earlier lanes / earlier rounds after it with B
+// independent compares. TAIL = false requires p + 32*B < L (every candidate is an interior point of the chain).
+constexpr int PB1 = 3;          // first round of a segment: 96 candidates (the average segment is ~45 cells)
+constexpr int PB2 = 7;          // later rounds: 224 candidates
+constexpr int PBMAX = PB2;
+
+__device__ __forceinline__ double dmin_(double a, double b) { return b < a ? b : a; }
+__device__ __forceinline__ double dmax_(double a, double b) { return b > a ? b : a; }
+__device__ __forceinline__ double scan_min_fast(double v, int lane) {
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const double t = __shfl_up_sync(FULL, v, o); if (lane >= o) v = dmin_(v, t); }
+    return v;
+}
+__device__ __forceinline__ double scan_max_fast(double v, int lane) {
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const double t = __shfl_up_sync(FULL, v, o); if (lane >= o) v = dmax_(v, t); }
+    return v;
+}
 
 // latest b (< limit) with x[b] == v, or -1
-__device__ __forceinline__ int latest_equal(const double (&x)[PB], double v, int limit) {
+template <int B>
+__device__ __forceinline__ int latest_equal(const double (&x)[B], double v, int limit) {
     int r = -1;
 #pragma unroll
-    for (int b = 0; b < PB; ++b) if (b < limit && x[b] == v) r = b;
+    for (int b = 0; b < B; ++b) if (b < limit && x[b] == v) r = b;
     return r;
+}
+
+// Returns true when a tube violation was found: the segment then ends at kend with value c + slope, leaving the
+// upper (isup) or lower tube edge. Otherwise the carried bounds (H, kH, Lw, kL) are updated.
+template <int B, bool TAIL>
+__device__ __forceinline__ bool taut_round(const double *__restrict__ S, const double *__restrict__ R, const int L,
+                                           const double lam, const int k0, const double s0, const int p, const int lane,
+                                           double &H, double &Lw, int &kH, int &kL, int &isup, double &slope, int &kend) {
+    const double INF = __longlong_as_double(0x7ff0000000000000LL);
+    const int kb = p + 1 + lane * B;
+    const double *__restrict__ Sp = S + kb;
+    const double *__restrict__ Rp = R + (kb - k0);
+    double hi[B], lo[B];
+    double hmin = INF, lmax = -INF;
+    unsigned m = 0;
+#pragma unroll
+    for (int b = 0; b < B; ++b) {
+        double h, l;
+        if (TAIL) {
+            const int k = kb + b;
+            h = INF; l = -INF;
+            if (k <= L) {
+                const double base = Sp[b] - s0;
+                const double lamk = (k == L) ? 0.0 : lam;
+                const double ri = Rp[b];
+                h = (base + lamk) * ri;
+                l = (base - lamk) * ri;
+            }
+        } else {
+            const double base = Sp[b] - s0;
+            const double ri = Rp[b];
+            h = (base + lam) * ri;
+            l = (base - lam) * ri;
+        }
+        hi[b] = h; lo[b] = l;
+        if ((l > hmin) || (h < lmax)) m |= 1u << b;
+        hmin = dmin_(hmin, h); lmax = dmax_(lmax, l);
+    }
+    const double Hs = scan_min_fast(hmin, lane), Ls = scan_max_fast(lmax, lane);
+    double Hx = __shfl_up_sync(FULL, Hs, 1), Lx = __shfl_up_sync(FULL, Ls, 1);
+    if (lane == 0) { Hx = INF; Lx = -INF; }
+    Hx = dmin_(Hx, H); Lx = dmax_(Lx, Lw);
+#pragma unroll
+    for (int b = 0; b < B; ++b)
+        if ((lo[b] > Hx) || (hi[b] < Lx)) m |= 1u << b;
+    const unsigned mask = __ballot_sync(FULL, m != 0u);
+    if (mask == 0u) {
+        const double nH = __shfl_sync(FULL, Hs, 31), nL = __shfl_sync(FULL, Ls, 31);
+        if (nH <= H) {
+            H = nH;
+            const int src = 31 - __clz(__ballot_sync(FULL, hmin == nH));
+            kH = __shfl_sync(FULL, kb + latest_equal<B>(hi, nH, B), src);
+        }
+        if (nL >= Lw) {
+            Lw = nL;
+            const int src = 31 - __clz(__ballot_sync(FULL, lmax == nL));
+            kL = __shfl_sync(FULL, kb + latest_equal<B>(lo, nL, B), src);
+        }
+        return false;
+    }
+    const int fb = __ffs(mask) - 1;
+    // lane fb: first violating candidate, the bound it violates and where that bound was attained
+    int up = 0, ke = -1;
+    double sl = 0.0;
+    if (lane == fb) {
+        const int bv = __ffs(m) - 1;
+        double pmH = INF, pmL = -INF, lv = 0.0;
+#pragma unroll
+        for (int b = 0; b < B; ++b) {
+            if (b < bv) { pmH = dmin_(pmH, hi[b]); pmL = dmax_(pmL, lo[b]); }
+            if (b == bv) lv = lo[b];
+        }
+        const double bH = dmin_(Hx, pmH), bL = dmax_(Lx, pmL);
+        up = lv > bH;
+        if (up) { sl = bH; if (pmH <= Hx) ke = kb + latest_equal<B>(hi, sl, bv); }
+        else    { sl = bL; if (pmL >= Lx) ke = kb + latest_equal<B>(lo, sl, bv); }
+    }
+    up = __shfl_sync(FULL, up, fb);
+    sl = __shfl_sync(FULL, sl, fb);
+    ke = __shfl_sync(FULL, ke, fb);
+    if (ke < 0) { // attained in an earlier lane of this round, else in an earlier round
+        const unsigned eq = __ballot_sync(FULL, lane < fb && (up ? hmin : lmax) == sl);
+        if (eq) {
+            const int src = 31 - __clz(eq);
+            ke = __shfl_sync(FULL, kb + (up ? latest_equal<B>(hi, sl, B) : latest_equal<B>(lo, sl, B)), src);
+        } else ke = up ? kH : kL;
+    }
+    isup = up; slope = sl; kend = ke;
+    return true;
 }
 
 __device__ __forceinline__ void taut_string_warp(double *__restrict__ S, const int L, const double lam, const double c,
@@ -142,93 +247,31 @@ __device__ __forceinline__ void taut_string_warp(double *__restrict__ S, const i
         double H = INF, Lw = -INF; // running min of hi / max of lo over the rounds already examined
         int kH = k0, kL = k0;      // where they were attained (latest on ties, as gfl_tf.c keeps the later knot)
         int p = k0;
-        for (;;) {
-            const int kb = p + 1 + lane * PB;
-            double hi[PB], lo[PB];
-            double hmin = INF, lmax = -INF;
-            unsigned upm = 0, dnm = 0;
-#pragma unroll
-            for (int b = 0; b < PB; ++b) {
-                const int k = kb + b;
-                double h = INF, l = -INF;
-                if (k <= L) {
-                    const double base = S[k] - s0;
-                    const double lamk = (k == L) ? 0.0 : lam;
-                    const double ri = R[k - k0];
-                    h = (base + lamk) * ri;
-                    l = (base - lamk) * ri;
-                }
-                hi[b] = h; lo[b] = l;
-                if (l > hmin) upm |= 1u << b;
-                if (h < lmax) dnm |= 1u << b;
-                hmin = fmin(hmin, h); lmax = fmax(lmax, l);
-            }
-            const double Hs = scan_min_incl(hmin, lane), Ls = scan_max_incl(lmax, lane);
-            double Hx = __shfl_up_sync(FULL, Hs, 1), Lx = __shfl_up_sync(FULL, Ls, 1);
-            if (lane == 0) { Hx = INF; Lx = -INF; }
-            Hx = fmin(Hx, H); Lx = fmax(Lx, Lw);
-#pragma unroll
-            for (int b = 0; b < PB; ++b) {
-                if (lo[b] > Hx) upm |= 1u << b;
-                if (hi[b] < Lx) dnm |= 1u << b;
-            }
-            const unsigned anym = upm | dnm;
-            const unsigned mask = __ballot_sync(FULL, anym != 0u);
-            if (mask == 0u) {
-                if (p + PW >= L) { // candidate k = L was examined: the last segment runs to the end of the chain
-                    const double val = c + ((S[L] - s0) + 0.0) * R[L - k0];
-                    __syncwarp();
-                    for (int i = k0 + lane; i < L; i += 32) S[i] = val;
-                    k0 = L;
-                    break;
-                }
-                const double nH = __shfl_sync(FULL, Hs, 31), nL = __shfl_sync(FULL, Ls, 31);
-                if (nH <= H) {
-                    H = nH;
-                    const int src = 31 - __clz(__ballot_sync(FULL, hmin == nH));
-                    kH = __shfl_sync(FULL, kb + latest_equal(hi, nH, PB), src);
-                }
-                if (nL >= Lw) {
-                    Lw = nL;
-                    const int src = 31 - __clz(__ballot_sync(FULL, lmax == nL));
-                    kL = __shfl_sync(FULL, kb + latest_equal(lo, nL, PB), src);
-                }
-                p += PW;
-                continue;
-            }
-            const int fb = __ffs(mask) - 1;
-            // lane fb: first violating candidate, the bound it violates and where that bound was attained
-            int isup = 0, kend = -1;
-            double slope = 0.0;
-            if (lane == fb) {
-                const int bv = __ffs(anym) - 1;
-                isup = (upm >> bv) & 1u;
-                double pm = isup ? INF : -INF;
-#pragma unroll
-                for (int b = 0; b < PB; ++b)
-                    if (b < bv) pm = isup ? fmin(pm, hi[b]) : fmax(pm, lo[b]);
-                if (isup) { slope = fmin(Hx, pm); if (pm <= Hx) kend = kb + latest_equal(hi, slope, bv); }
-                else      { slope = fmax(Lx, pm); if (pm >= Lx) kend = kb + latest_equal(lo, slope, bv); }
-            }
-            isup = __shfl_sync(FULL, isup, fb);
-            slope = __shfl_sync(FULL, slope, fb);
-            kend = __shfl_sync(FULL, kend, fb);
-            if (kend < 0) { // attained in an earlier lane of this round, else in an earlier round
-                const unsigned eq = __ballot_sync(FULL, lane < fb && (isup ? hmin : lmax) == slope);
-                if (eq) {
-                    const int src = 31 - __clz(eq);
-                    kend = __shfl_sync(FULL, kb + (isup ? latest_equal(hi, slope, PB) : latest_equal(lo, slope, PB)), src);
-                } else kend = isup ? kH : kL;
-            }
-            const double snext = S[kend] + (isup ? lam : -lam);
-            const double val = c + slope;
-            __syncwarp();
-            for (int i = k0 + lane; i < kend; i += 32) S[i] = val;
-            __syncwarp();
-            s0 = snext;
-            k0 = kend;
-            break;
+        int isup = 0, kend = 0;
+        double slope = 0.0;
+        bool viol;
+        // first round: narrow
+        if (p + 32 * PB1 < L) viol = taut_round<PB1, false>(S, R, L, lam, k0, s0, p, lane, H, Lw, kH, kL, isup, slope, kend);
+        else                  viol = taut_round<PB1, true>(S, R, L, lam, k0, s0, p, lane, H, Lw, kH, kL, isup, slope, kend);
+        p += 32 * PB1;
+        while (!viol && p < L) {
+            if (p + 32 * PB2 < L) viol = taut_round<PB2, false>(S, R, L, lam, k0, s0, p, lane, H, Lw, kH, kL, isup, slope, kend);
+            else                  viol = taut_round<PB2, true>(S, R, L, lam, k0, s0, p, lane, H, Lw, kH, kL, isup, slope, kend);
+            p += 32 * PB2;
         }
+        double val, snext = 0.0;
+        if (!viol) { // candidate k = L was examined without violation: the last segment runs to the end of the chain
+            val = c + ((S[L] - s0) + 0.0) * R[L - k0];
+            kend = L;
+        } else {
+            snext = S[kend] + (isup ? lam : -lam);
+            val = c + slope;
+        }
+        __syncwarp();
+        for (int i = k0 + lane; i < kend; i += 32) S[i] = val;
+        __syncwarp();
+        s0 = snext;
+        k0 = kend;
     }
     __syncwarp();
 }
@@ -276,7 +319,7 @@ k_prox(Grid g, GflCtl *__restrict__ ctl, const double *__restrict__ beta, const 
             double carry = 0.0;
             for (int p = 0; p < L; p += PW) {
                 const int kb = p + lane * PB;
-                double t[PB];
+                double t[PBMAX];
                 double run = 0.0;
 #pragma unroll
                 for (int b = 0; b < PB; ++b) { const int k = kb + b; run += (k < L) ? S[k + 1] - c : 0.0; t[b] = run; }
