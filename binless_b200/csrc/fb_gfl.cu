@@ -17,6 +17,8 @@
 #include "fb_gfl.cuh"
 #include <algorithm>
 #include <cmath>
+#include <cstdio>
+#include <cstdlib>
 #include <vector>
 
 namespace fb {
@@ -279,7 +281,7 @@ __device__ __forceinline__ void taut_string_warp(double *__restrict__ S, const i
 __global__ void __launch_bounds__(32 * PROX_MAX_WARPS, 1)
 k_prox(Grid g, GflCtl *__restrict__ ctl, const double *__restrict__ beta, const double *__restrict__ betaT,
        double *__restrict__ zr, double *__restrict__ ur, double *__restrict__ zc, double *__restrict__ uc,
-       double *__restrict__ partials, int stride, int rlen) {
+       double *__restrict__ partials, int stride, int rlen, long long *__restrict__ trace) {
     if (ctl->done) return;
     extern __shared__ double smem[];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -296,6 +298,8 @@ k_prox(Grid g, GflCtl *__restrict__ ctl, const double *__restrict__ beta, const 
     while (q < nchains) {
         int qnext = 0;
         if (lane == 0) qnext = atomicAdd(&ctl->next_chain, 1); // consumed after this chain: latency hidden
+        long long t0 = 0, t1 = 0, t2 = 0;
+        if (trace) t0 = clock64();
         int dir, idx, L; int64_t start;
         g.chain(q, dir, idx, L, start);
         const double *__restrict__ B = (dir == 0 ? beta : betaT) + start;
@@ -331,7 +335,9 @@ k_prox(Grid g, GflCtl *__restrict__ ctl, const double *__restrict__ beta, const 
             }
             if (lane == 0) S[0] = 0.0;
             __syncwarp();
+            if (trace) t1 = clock64();
             taut_string_warp(S, L, lam, c, R, lane);
+            if (trace) t2 = clock64();
         }
         __syncwarp();
         // u += beta - z, residual sums (gfl_graph_fl.c:306-365)
@@ -359,6 +365,10 @@ k_prox(Grid g, GflCtl *__restrict__ ctl, const double *__restrict__ beta, const 
         }
         ap = warp_sum(ap); ad = warp_sum(ad);
         if (lane == 0) { partials[2 * q] = ap; partials[2 * q + 1] = ad; }
+        if (trace && lane == 0) {
+            unsigned smid; asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+            trace[4 * q] = t1 - t0; trace[4 * q + 1] = t2 - t1; trace[4 * q + 2] = clock64() - t2; trace[4 * q + 3] = ((long long)smid << 48) | (t0 & 0xffffffffffffLL);
+        }
         __syncwarp();
         q = __shfl_sync(FULL, qnext, 0);
     }
@@ -476,6 +486,7 @@ GflSolver::GflSolver(int nbins, unsigned maxdiag, cudaStream_t stream) : nbins_(
         prox_grid_ = std::min(n_sm_, (g_.nchains() + prox_warps_ - 1) / prox_warps_);
     }
     ctl_.alloc(1);
+    if (std::getenv("FB_PROX_TRACE")) { trace_.alloc(4 * (size_t)g_.nchains()); trace_.zero(); }
     FB_CUDA(cudaMallocHost((void **)&h_ctl_, sizeof(GflCtl)));
     FB_CUDA(cudaEventCreate(&ev0_)); FB_CUDA(cudaEventCreate(&ev1_));
     reset();
@@ -498,7 +509,7 @@ void GflSolver::iteration(const double *y, const double *w, int parity) {
     dim3 tb(TILE, 8), tg((g_.n + TILE - 1) / TILE, (g_.n + TILE - 1) / TILE);
     k_beta<<<tg, tb, 0, st_>>>(g_, ctl_.p, y, w, zr_.p, ur_.p, zc_.p, uc_.p, beta_.p, betaT_.p);
     k_prox<<<prox_grid_, 32 * prox_warps_, prox_smem_, st_>>>(g_, ctl_.p, beta_.p, betaT_.p, zr_.p, ur_.p, zc_.p, uc_.p,
-                                                             partials_.p, prox_stride_, prox_rlen_);
+                                                             partials_.p, prox_stride_, prox_rlen_, trace_.p);
     k_ctl<<<1, CTL_THREADS, 0, st_>>>(ctl_.p, partials_.p, n_partials_, g_.ncells, 2 * g_.ncells - 2);
     kernel_launches += 3;
 }
@@ -549,6 +560,11 @@ int GflSolver::optimize(const double *d_y_tri, const double *d_w_tri, double lam
     FB_CUDA(cudaEventRecord(ev1_, st_));
     FB_CUDA(cudaEventSynchronize(ev1_));
     FB_CUDA(cudaEventElapsedTime(&ms_last, ev0_, ev1_));
+    if (trace_.p) { // development aid (FB_PROX_TRACE=file): per-chain cycle counts of the last executed k_prox
+        std::vector<long long> h(trace_.n);
+        FB_CUDA(cudaMemcpy(h.data(), trace_.p, trace_.n * sizeof(long long), cudaMemcpyDeviceToHost));
+        if (FILE *f = std::fopen(std::getenv("FB_PROX_TRACE"), "wb")) { std::fwrite(h.data(), sizeof(long long), h.size(), f); std::fclose(f); }
+    }
     return last_steps;
 }
 

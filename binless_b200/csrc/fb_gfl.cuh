@@ -92,6 +92,7 @@ private:
     DevBuf<double> beta_, betaT_, zr_, ur_, zc_, uc_, yband_, wband_, fillavg_;
     DevBuf<double> partials_;
     DevBuf<GflCtl> ctl_;
+    DevBuf<long long> trace_;         // FB_PROX_TRACE development aid
     GflCtl *h_ctl_ = nullptr;          // pinned
     const double *y_tri_ = nullptr, *w_tri_ = nullptr;
     int n_partials_ = 0;
