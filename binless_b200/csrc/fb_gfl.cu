@@ -28,8 +28,7 @@ namespace {
 constexpr int TILE = 32;
 constexpr int CTL_THREADS = 1024;
 constexpr int POLL_BATCH = 8;
-constexpr int PROX_MAX_WARPS = 16;
-constexpr int PB = 7, PW = 32 * PB;   // run length of the blocked prefix-sum pass
+constexpr int PROX_MAX_TEAMS = 10;    // two warps per chain; 704 threads leave 88 registers per thread
 constexpr unsigned FULL = 0xffffffffu;
 
 // --------------------------------------------------------------------------
@@ -121,13 +120,21 @@ __device__ __forceinline__ double scan_sum_incl(double v, int lane) {
     return v;
 }
 
+// --------------------------------------------------------------------------
+// Two warps per chain ("team"), one working from each end. The 1-D fused-lasso minimiser is unique, and the taut
+// string of the mirrored chain is the mirror image of the taut string, so the LEFT warp determines the knots in
+// increasing order while the RIGHT warp determines them in decreasing order (on S'(k) = S[L] - S[L-k], the prefix
+// sums of the reversed chain). A knot found by the other warp is a point the string is known to pass through:
+// it becomes this warp's fixed end point (offset aEnd = -/+ lam or 0 instead of the tube). The warps advance in
+// lock step, one round each between two named barriers, until the finished parts meet.
+//
 // One round examines 32*B consecutive candidates, lane l owning the B consecutive ones starting at
 // p + 1 + l*B (B odd: conflict-free 8-byte shared-memory accesses). Violations against the lane-local running
 // bounds are found before the warp scan, those against earlier lanes / earlier rounds after it with B
-// independent compares. TAIL = false requires p + 32*B < L (every candidate is an interior point of the chain).
-constexpr int PB1 = 3;          // first round of a segment: 96 candidates (the average segment is ~45 cells)
-constexpr int PB2 = 7;          // later rounds: 224 candidates
-constexpr int PBMAX = PB2;
+// independent compares. TAIL = false requires p + 32*B < kEnd (every candidate is an interior point).
+// --------------------------------------------------------------------------
+constexpr int PBR = 5;          // 160 candidates per round (the average segment is ~45 cells)
+constexpr int PB = 7, PW = 32 * PB;   // run length of the blocked prefix-sum pass
 
 __device__ __forceinline__ double dmin_(double a, double b) { return b < a ? b : a; }
 __device__ __forceinline__ double dmax_(double a, double b) { return b > a ? b : a; }
@@ -143,69 +150,99 @@ __device__ __forceinline__ double scan_max_fast(double v, int lane) {
 }
 
 // latest b (< limit) with x[b] == v, or -1
-template <int B>
-__device__ __forceinline__ int latest_equal(const double (&x)[B], double v, int limit) {
+__device__ __forceinline__ int latest_equal(const double (&x)[PBR], double v, int limit) {
+    constexpr int B = PBR;
     int r = -1;
 #pragma unroll
     for (int b = 0; b < B; ++b) if (b < limit && x[b] == v) r = b;
     return r;
 }
 
+// The chain as one warp sees it: frame coordinate k in [0, L], value sgn * S[idx(k)] + off.
+struct Frame {
+    const double *S;   // prefix sums of the chain, S[0..L]
+    int L, dir;        // dir 0: left warp (k -> S[k]); dir 1: right warp (k -> S[L] - S[L-k])
+    double SL;
+    __device__ __forceinline__ double at(int k) const { return dir ? SL - S[L - k] : S[k]; }
+};
+
+// Search state of one segment (frame coordinates)
+struct Seg {
+    int k0; double s0;          // start of the segment being searched: the string passes through (k0, s0)
+    int p;                      // candidates up to p have been examined
+    double H, Lw; int kH, kL;   // running min of hi / max of lo and where they were attained (latest on ties)
+};
+
 // Returns true when a tube violation was found: the segment then ends at kend with value c + slope, leaving the
-// upper (isup) or lower tube edge. Otherwise the carried bounds (H, kH, Lw, kL) are updated.
-template <int B, bool TAIL>
-__device__ __forceinline__ bool taut_round(const double *__restrict__ S, const double *__restrict__ R, const int L,
-                                           const double lam, const int k0, const double s0, const int p, const int lane,
-                                           double &H, double &Lw, int &kH, int &kL, int &isup, double &slope, int &kend) {
+// upper (isup) or lower tube edge. Otherwise the carried bounds are updated. One instantiation only, loops that
+// are not on the critical path are not unrolled: the team kernel is instruction-cache bound otherwise.
+constexpr int B = PBR;
+__device__ __forceinline__ bool taut_round(const Frame &f, const double *__restrict__ R, const double lam, Seg &g,
+                                           const int kEnd, const double aEnd, const int lane,
+                                           int &isup, double &slope, int &kend) {
     const double INF = __longlong_as_double(0x7ff0000000000000LL);
-    const int kb = p + 1 + lane * B;
-    const double *__restrict__ Sp = S + kb;
-    const double *__restrict__ Rp = R + (kb - k0);
+    const int kb = g.p + 1 + lane * B;
+    const double sgn = f.dir ? -1.0 : 1.0;
+    const double off = f.dir ? f.SL - g.s0 : -g.s0;
     double hi[B], lo[B];
     double hmin = INF, lmax = -INF;
     unsigned m = 0;
+    if (g.p + 32 * B < kEnd) { // every candidate is an interior point of the chain
+        const double *__restrict__ Rp = R + (kb - g.k0);
+        double sv[B];
+        if (f.dir) {
+            const double *__restrict__ Sq = f.S + (f.L - kb);
 #pragma unroll
-    for (int b = 0; b < B; ++b) {
-        double h, l;
-        if (TAIL) {
-            const int k = kb + b;
-            h = INF; l = -INF;
-            if (k <= L) {
-                const double base = Sp[b] - s0;
-                const double lamk = (k == L) ? 0.0 : lam;
-                const double ri = Rp[b];
-                h = (base + lamk) * ri;
-                l = (base - lamk) * ri;
-            }
+            for (int b = 0; b < B; ++b) sv[b] = Sq[-b];
         } else {
-            const double base = Sp[b] - s0;
-            const double ri = Rp[b];
-            h = (base + lam) * ri;
-            l = (base - lam) * ri;
+            const double *__restrict__ Sq = f.S + kb;
+#pragma unroll
+            for (int b = 0; b < B; ++b) sv[b] = Sq[b];
         }
-        hi[b] = h; lo[b] = l;
-        if ((l > hmin) || (h < lmax)) m |= 1u << b;
-        hmin = dmin_(hmin, h); lmax = dmax_(lmax, l);
+#pragma unroll
+        for (int b = 0; b < B; ++b) {
+            const double base = __fma_rn(sgn, sv[b], off);
+            const double ri = Rp[b];
+            const double h = (base + lam) * ri, l = (base - lam) * ri;
+            hi[b] = h; lo[b] = l;
+            if ((l > hmin) || (h < lmax)) m |= 1u << b;
+            hmin = dmin_(hmin, h); lmax = dmax_(lmax, l);
+        }
+    } else {                   // the fixed end point kEnd is among the candidates; those beyond it do not exist
+#pragma unroll
+        for (int b = 0; b < B; ++b) {
+            const int k = kb + b;
+            const int kc = k < kEnd ? k : kEnd;
+            const double base = __fma_rn(sgn, f.S[f.dir ? f.L - kc : kc], off);
+            const double ri = R[kc - g.k0];
+            const bool fixed = (k == kEnd);      // a point of the string, not a tube
+            double h = (base + (fixed ? aEnd : lam)) * ri;
+            double l = (base - (fixed ? -aEnd : lam)) * ri;
+            if (k > kEnd) { h = INF; l = -INF; }
+            hi[b] = h; lo[b] = l;
+            if ((l > hmin) || (h < lmax)) m |= 1u << b;
+            hmin = dmin_(hmin, h); lmax = dmax_(lmax, l);
+        }
     }
     const double Hs = scan_min_fast(hmin, lane), Ls = scan_max_fast(lmax, lane);
     double Hx = __shfl_up_sync(FULL, Hs, 1), Lx = __shfl_up_sync(FULL, Ls, 1);
     if (lane == 0) { Hx = INF; Lx = -INF; }
-    Hx = dmin_(Hx, H); Lx = dmax_(Lx, Lw);
+    Hx = dmin_(Hx, g.H); Lx = dmax_(Lx, g.Lw);
 #pragma unroll
     for (int b = 0; b < B; ++b)
         if ((lo[b] > Hx) || (hi[b] < Lx)) m |= 1u << b;
     const unsigned mask = __ballot_sync(FULL, m != 0u);
     if (mask == 0u) {
         const double nH = __shfl_sync(FULL, Hs, 31), nL = __shfl_sync(FULL, Ls, 31);
-        if (nH <= H) {
-            H = nH;
+        if (nH <= g.H) {
+            g.H = nH;
             const int src = 31 - __clz(__ballot_sync(FULL, hmin == nH));
-            kH = __shfl_sync(FULL, kb + latest_equal<B>(hi, nH, B), src);
+            g.kH = __shfl_sync(FULL, kb + latest_equal(hi, nH, B), src);
         }
-        if (nL >= Lw) {
-            Lw = nL;
+        if (nL >= g.Lw) {
+            g.Lw = nL;
             const int src = 31 - __clz(__ballot_sync(FULL, lmax == nL));
-            kL = __shfl_sync(FULL, kb + latest_equal<B>(lo, nL, B), src);
+            g.kL = __shfl_sync(FULL, kb + latest_equal(lo, nL, B), src);
         }
         return false;
     }
@@ -223,8 +260,8 @@ __device__ __forceinline__ bool taut_round(const double *__restrict__ S, const d
         }
         const double bH = dmin_(Hx, pmH), bL = dmax_(Lx, pmL);
         up = lv > bH;
-        if (up) { sl = bH; if (pmH <= Hx) ke = kb + latest_equal<B>(hi, sl, bv); }
-        else    { sl = bL; if (pmL >= Lx) ke = kb + latest_equal<B>(lo, sl, bv); }
+        if (up) { sl = bH; if (pmH <= Hx) ke = kb + latest_equal(hi, sl, bv); }
+        else    { sl = bL; if (pmL >= Lx) ke = kb + latest_equal(lo, sl, bv); }
     }
     up = __shfl_sync(FULL, up, fb);
     sl = __shfl_sync(FULL, sl, fb);
@@ -233,144 +270,190 @@ __device__ __forceinline__ bool taut_round(const double *__restrict__ S, const d
         const unsigned eq = __ballot_sync(FULL, lane < fb && (up ? hmin : lmax) == sl);
         if (eq) {
             const int src = 31 - __clz(eq);
-            ke = __shfl_sync(FULL, kb + (up ? latest_equal<B>(hi, sl, B) : latest_equal<B>(lo, sl, B)), src);
-        } else ke = up ? kH : kL;
+            ke = __shfl_sync(FULL, kb + (up ? latest_equal(hi, sl, B) : latest_equal(lo, sl, B)), src);
+        } else ke = up ? g.kH : g.kL;
     }
     isup = up; slope = sl; kend = ke;
     return true;
 }
 
-__device__ __forceinline__ void taut_string_warp(double *__restrict__ S, const int L, const double lam, const double c,
-                                                 const double *__restrict__ R, const int lane) {
+__device__ __forceinline__ void team_sync(int bar) { asm volatile("bar.sync %0, 64;" ::"r"(bar) : "memory"); }
+
+__device__ __forceinline__ void seg_reset(Seg &g) {
     const double INF = __longlong_as_double(0x7ff0000000000000LL);
-    int k0 = 0;
-    double s0 = 0.0;
-    while (k0 < L) {
-        double H = INF, Lw = -INF; // running min of hi / max of lo over the rounds already examined
-        int kH = k0, kL = k0;      // where they were attained (latest on ties, as gfl_tf.c keeps the later knot)
-        int p = k0;
-        int isup = 0, kend = 0;
-        double slope = 0.0;
-        bool viol;
-        // first round: narrow
-        if (p + 32 * PB1 < L) viol = taut_round<PB1, false>(S, R, L, lam, k0, s0, p, lane, H, Lw, kH, kL, isup, slope, kend);
-        else                  viol = taut_round<PB1, true>(S, R, L, lam, k0, s0, p, lane, H, Lw, kH, kL, isup, slope, kend);
-        p += 32 * PB1;
-        while (!viol && p < L) {
-            if (p + 32 * PB2 < L) viol = taut_round<PB2, false>(S, R, L, lam, k0, s0, p, lane, H, Lw, kH, kL, isup, slope, kend);
-            else                  viol = taut_round<PB2, true>(S, R, L, lam, k0, s0, p, lane, H, Lw, kH, kL, isup, slope, kend);
-            p += 32 * PB2;
-        }
-        double val, snext = 0.0;
-        if (!viol) { // candidate k = L was examined without violation: the last segment runs to the end of the chain
-            val = c + ((S[L] - s0) + 0.0) * R[L - k0];
-            kend = L;
-        } else {
-            snext = S[kend] + (isup ? lam : -lam);
-            val = c + slope;
-        }
-        __syncwarp();
-        for (int i = k0 + lane; i < kend; i += 32) S[i] = val;
-        __syncwarp();
-        s0 = snext;
-        k0 = kend;
-    }
-    __syncwarp();
+    g.p = g.k0; g.H = INF; g.Lw = -INF; g.kH = g.k0; g.kL = g.k0;
 }
 
-__global__ void __launch_bounds__(32 * PROX_MAX_WARPS, 1)
+// Lock-step taut string of one chain by the two warps of a team. S holds the prefix sums S[0..L] on entry; on
+// return cell i of the solution is at S[i] for i < split (written by the left warp) and at S[i+1] for i >= split.
+__device__ __forceinline__ int taut_string_team(double *__restrict__ S, volatile int *__restrict__ ti, const int L,
+                                                const double lam, const double c, const double *__restrict__ R,
+                                                const int side, const int lane, const int bar, int &nrounds) {
+    Frame f; f.S = S; f.L = L; f.dir = side; f.SL = S[L];
+    Seg sg; sg.k0 = 0; sg.s0 = 0.0; seg_reset(sg);
+    int dL = 0, dR = L;      // cells [0, dL) and [dR, L) are finished (original coordinates)
+    int aL = 0, aR = 0;      // sign of the tube edge each warp's current segment starts from (own frame)
+    while (dL < dR) {
+        const int kEnd = side ? L - dL : dR;
+        const double aEnd = -(double)(side ? aL : aR) * lam;   // the sign flips under mirroring
+        if (kEnd <= sg.p) seg_reset(sg);                               // the other warp's knot moved inside the scanned range
+        int isup = 0, kend = 0;
+        double slope = 0.0;
+        const bool viol = taut_round(f, R, lam, sg, kEnd, aEnd, lane, isup, slope, kend);
+        sg.p += 32 * PBR;
+        ++nrounds;
+        int status = 0, asign = 0;
+        double val = 0.0, s0n = 0.0;
+        if (viol) {
+            status = 1; asign = isup ? 1 : -1;
+            val = c + slope;
+            s0n = f.at(kend) + (isup ? lam : -lam);
+        } else if (sg.p >= kEnd) { // the fixed end point was examined without violation: the segment runs up to it
+            status = 1; kend = kEnd;
+            val = c + ((f.at(kEnd) - sg.s0) + aEnd) * R[kEnd - sg.k0];
+        }
+        if (lane == 0) { ti[side * 4] = status; ti[side * 4 + 1] = side ? L - kend : kend; ti[side * 4 + 2] = asign; }
+        team_sync(bar);
+        const int ost = ti[(1 - side) * 4], oe = ti[(1 - side) * 4 + 1], oa = ti[(1 - side) * 4 + 2];
+        int eL = dL, eR = dR;
+        if (side ? ost : status) eL = side ? oe : kend;
+        if (side ? status : ost) eR = side ? L - kend : oe;
+        if (eR < eL) eR = eL;                                    // the left warp wins an overlap
+        if (status) {
+            if (side == 0) {
+#pragma unroll 1
+                for (int i = dL + lane; i < eL; i += 32) S[i] = val;
+            } else {
+#pragma unroll 1
+                for (int i = eR + lane; i < dR; i += 32) S[i + 1] = val;
+            }
+            sg.k0 = kend; sg.s0 = s0n; seg_reset(sg);
+            if (side) aR = asign; else aL = asign;
+        }
+        if (ost) { if (side) aL = oa; else aR = oa; }
+        dL = eL; dR = eR;
+        team_sync(bar);
+    }
+    return dL;
+}
+
+__global__ void __launch_bounds__(64 * PROX_MAX_TEAMS, 1)
 k_prox(Grid g, GflCtl *__restrict__ ctl, const double *__restrict__ beta, const double *__restrict__ betaT,
        double *__restrict__ zr, double *__restrict__ ur, double *__restrict__ zc, double *__restrict__ uc,
        double *__restrict__ partials, int stride, int rlen, long long *__restrict__ trace) {
     if (ctl->done) return;
     extern __shared__ double smem[];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int team = wid >> 1, side = wid & 1, bar = 1 + team;
     double *__restrict__ R = smem;                                   // R[m] = 1/m, m = 1..rlen-1
-    double *__restrict__ S = smem + rlen + (size_t)wid * stride;
+    double *__restrict__ S = smem + rlen + (size_t)team * stride;
+    volatile int *ti = reinterpret_cast<volatile int *>(S + (stride - 8)); // team mailbox: 16 ints
     for (int m = threadIdx.x; m < rlen; m += blockDim.x) R[m] = m ? 1.0 / (double)m : 0.0;
     __syncthreads();
     const double alpha = ctl->alpha;
     const double lam = ctl->lam / (alpha / 2.0);
     const int nchains = g.nchains();
-    int q = 0;
-    if (lane == 0) q = atomicAdd(&ctl->next_chain, 1);
-    q = __shfl_sync(FULL, q, 0);
+    if (side == 0 && lane == 0) ti[8] = atomicAdd(&ctl->next_chain, 1);
+    team_sync(bar);
+    int q = ti[8];
     while (q < nchains) {
         int qnext = 0;
-        if (lane == 0) qnext = atomicAdd(&ctl->next_chain, 1); // consumed after this chain: latency hidden
+        if (side == 0 && lane == 0) qnext = atomicAdd(&ctl->next_chain, 1); // published after this chain: latency hidden
         long long t0 = 0, t1 = 0, t2 = 0;
+        int nrounds = 0;
         if (trace) t0 = clock64();
         int dir, idx, L; int64_t start;
         g.chain(q, dir, idx, L, start);
         const double *__restrict__ B = (dir == 0 ? beta : betaT) + start;
         double *__restrict__ Z = (dir == 0 ? zr : zc) + start;
         double *__restrict__ U = (dir == 0 ? ur : uc) + start;
+        const int half = (L + 1) >> 1;
+        const int lo_ = side ? half : 0, hi_ = side ? L : half;    // the cells this warp stages and writes back
+        const bool copy = (lam == 0.0 || L == 1);                   // tf_dp_weight copies y (gfl_tf.c:210-215)
+        double c = 0.0;
+        if (!copy && side) c = __ldcg(B) + __ldcg(U);
         // stage v = beta + u at S[k+1], coalesced, 8 loads per array in flight
-        for (int p = 0; p < L; p += 256) {
+#pragma unroll 1
+        for (int p = lo_; p < hi_; p += 256) {
             double vb[8], vu[8];
 #pragma unroll
-            for (int b = 0; b < 8; ++b) { const int k = p + 32 * b + lane; vb[b] = k < L ? B[k] : 0.0; vu[b] = k < L ? U[k] : 0.0; }
+            for (int b = 0; b < 8; ++b) { const int k = p + 32 * b + lane; vb[b] = k < hi_ ? __ldcg(B + k) : 0.0; vu[b] = k < hi_ ? __ldcg(U + k) : 0.0; }
 #pragma unroll
-            for (int b = 0; b < 8; ++b) { const int k = p + 32 * b + lane; if (k < L) S[k + 1] = vb[b] + vu[b]; }
+            for (int b = 0; b < 8; ++b) { const int k = p + 32 * b + lane; if (k < hi_) S[k + 1] = vb[b] + vu[b]; }
         }
         __syncwarp();
-        int so = 0; // solution at S[k + so]
-        if (lam == 0.0 || L == 1) { // tf_dp_weight copies y (gfl_tf.c:210-215)
-            so = 1;
-        } else {
-            // in-place prefix sums S[k+1] = sum_{i<=k} (v_i - c): lane-local runs of PB, one warp scan per 32*PB
-            const double c = S[1];
+        int split = 0; // cell i of the solution at S[i] for i < split, else at S[i + 1]
+        if (!copy) {
+            if (!side) c = S[1];
+            // in-place prefix sums of (v_i - c) over this warp's half: lane-local runs of PB, one warp scan per 32*PB
             double carry = 0.0;
-            for (int p = 0; p < L; p += PW) {
+#pragma unroll 1
+            for (int p = lo_; p < hi_; p += PW) {
                 const int kb = p + lane * PB;
-                double t[PBMAX];
+                double t[PB];
                 double run = 0.0;
 #pragma unroll
-                for (int b = 0; b < PB; ++b) { const int k = kb + b; run += (k < L) ? S[k + 1] - c : 0.0; t[b] = run; }
+                for (int b = 0; b < PB; ++b) { const int k = kb + b; run += (k < hi_) ? S[k + 1] - c : 0.0; t[b] = run; }
                 const double incl = scan_sum_incl(run, lane);
                 const double off = (incl - run) + carry;
 #pragma unroll
-                for (int b = 0; b < PB; ++b) { const int k = kb + b; if (k < L) S[k + 1] = t[b] + off; }
+                for (int b = 0; b < PB; ++b) { const int k = kb + b; if (k < hi_) S[k + 1] = t[b] + off; }
                 carry += __shfl_sync(FULL, incl, 31);
             }
-            if (lane == 0) S[0] = 0.0;
-            __syncwarp();
+            if (!side && lane == 0) S[0] = 0.0;
+            team_sync(bar);
+            if (side) { // the right half continues the left half's sums
+                const double off = S[half];
+#pragma unroll 1
+                for (int p = lo_; p < hi_; p += 128) {
+                    double t[4];
+#pragma unroll
+                    for (int b = 0; b < 4; ++b) { const int k = p + 32 * b + lane; t[b] = k < hi_ ? S[k + 1] : 0.0; }
+#pragma unroll
+                    for (int b = 0; b < 4; ++b) { const int k = p + 32 * b + lane; if (k < hi_) S[k + 1] = t[b] + off; }
+                }
+            }
+            team_sync(bar);
             if (trace) t1 = clock64();
-            taut_string_warp(S, L, lam, c, R, lane);
+            split = taut_string_team(S, ti, L, lam, c, R, side, lane, bar, nrounds);
             if (trace) t2 = clock64();
+        } else {
+            team_sync(bar);
         }
-        __syncwarp();
         // u += beta - z, residual sums (gfl_graph_fl.c:306-365)
         double ap = 0.0, ad = 0.0;
-        for (int p = 0; p < L; p += 128) {
-            double b4[4], u4[4], z4[4];
+#pragma unroll 1
+        for (int p = lo_; p < hi_; p += 256) {
+            double b8[8], u8[8], z8[8];
 #pragma unroll
-            for (int b = 0; b < 4; ++b) {
+            for (int b = 0; b < 8; ++b) {
                 const int k = p + 32 * b + lane;
-                b4[b] = k < L ? B[k] : 0.0; u4[b] = k < L ? U[k] : 0.0; z4[b] = k < L ? Z[k] : 0.0;
+                b8[b] = k < hi_ ? __ldcg(B + k) : 0.0; u8[b] = k < hi_ ? __ldcg(U + k) : 0.0; z8[b] = k < hi_ ? __ldcg(Z + k) : 0.0;
             }
 #pragma unroll
-            for (int b = 0; b < 4; ++b) {
+            for (int b = 0; b < 8; ++b) {
                 const int k = p + 32 * b + lane;
-                if (k < L) {
-                    const double z = S[k + so];
-                    const double r = b4[b] - z;
-                    U[k] = u4[b] + r;
-                    Z[k] = z;
+                if (k < hi_) {
+                    const double z = S[k < split ? k : k + 1];
+                    const double r = b8[b] - z;
+                    __stcg(U + k, u8[b] + r);
+                    __stcg(Z + k, z);
                     ap += r * r;
-                    const double dd = alpha * (z - z4[b]);
+                    const double dd = alpha * (z - z8[b]);
                     ad += dd * dd;
                 }
             }
         }
         ap = warp_sum(ap); ad = warp_sum(ad);
-        if (lane == 0) { partials[2 * q] = ap; partials[2 * q + 1] = ad; }
-        if (trace && lane == 0) {
+        if (lane == 0) { partials[2 * (2 * q + side)] = ap; partials[2 * (2 * q + side) + 1] = ad; }
+        if (trace && lane == 0 && side == 0) {
             unsigned smid; asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
-            trace[4 * q] = t1 - t0; trace[4 * q + 1] = t2 - t1; trace[4 * q + 2] = clock64() - t2; trace[4 * q + 3] = ((long long)smid << 48) | (t0 & 0xffffffffffffLL);
+            trace[4 * q] = t1 - t0; trace[4 * q + 1] = t2 - t1; trace[4 * q + 2] = clock64() - t2;
+            trace[4 * q + 3] = ((long long)smid << 48) | (long long)nrounds;
         }
-        __syncwarp();
-        q = __shfl_sync(FULL, qnext, 0);
+        if (side == 0 && lane == 0) ti[8] = qnext;
+        team_sync(bar); // both warps are done with S; the next chain is published
+        q = ti[8];
     }
 }
 
@@ -467,7 +550,7 @@ GflSolver::GflSolver(int nbins, unsigned maxdiag, cudaStream_t stream) : nbins_(
     const int64_t N = g_.ncells;
     beta_.alloc(N); betaT_.alloc(N); zr_.alloc(N); ur_.alloc(N); zc_.alloc(N); uc_.alloc(N);
     if (trapeze_) { yband_.alloc(N); wband_.alloc(N); fillavg_.alloc(1); }
-    n_partials_ = g_.nchains();
+    n_partials_ = 2 * g_.nchains(); // one (primal, dual) pair per warp of a team
     partials_.alloc(2 * (size_t)std::max(n_partials_, nbins));
     // k_prox: one warp per chain, the chain's prefix sums in shared memory (8 (Lmax + 1) bytes per warp)
     {
@@ -476,9 +559,9 @@ GflSolver::GflSolver(int nbins, unsigned maxdiag, cudaStream_t stream) : nbins_(
         FB_CUDA(cudaDeviceGetAttribute(&smem_max, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
         FB_CUDA(cudaDeviceGetAttribute(&n_sm_, cudaDevAttrMultiProcessorCount, dev));
         const int lmax = g_.row_len(0);
-        prox_stride_ = lmax + 2;
+        prox_stride_ = lmax + 2 + 8;   // S[0..L], one spare slot, 16-int team mailbox
         prox_rlen_ = lmax + 1;
-        prox_warps_ = std::min<int64_t>(PROX_MAX_WARPS, ((int64_t)smem_max / 8 - prox_rlen_) / (int64_t)prox_stride_);
+        prox_warps_ = std::min<int64_t>(PROX_MAX_TEAMS, ((int64_t)smem_max / 8 - prox_rlen_) / (int64_t)prox_stride_);
         if (prox_warps_ < 1) throw ArgError("chains longer than 14500 cells are not supported by this build of the fused-lasso prox");
         prox_warps_ = std::min(prox_warps_, std::max(1, (g_.nchains() + n_sm_ - 1) / n_sm_));
         prox_smem_ = ((size_t)prox_warps_ * prox_stride_ + prox_rlen_) * 8;
@@ -508,7 +591,7 @@ void GflSolver::iteration(const double *y, const double *w, int parity) {
     (void)parity;
     dim3 tb(TILE, 8), tg((g_.n + TILE - 1) / TILE, (g_.n + TILE - 1) / TILE);
     k_beta<<<tg, tb, 0, st_>>>(g_, ctl_.p, y, w, zr_.p, ur_.p, zc_.p, uc_.p, beta_.p, betaT_.p);
-    k_prox<<<prox_grid_, 32 * prox_warps_, prox_smem_, st_>>>(g_, ctl_.p, beta_.p, betaT_.p, zr_.p, ur_.p, zc_.p, uc_.p,
+    k_prox<<<prox_grid_, 64 * prox_warps_, prox_smem_, st_>>>(g_, ctl_.p, beta_.p, betaT_.p, zr_.p, ur_.p, zc_.p, uc_.p,
                                                              partials_.p, prox_stride_, prox_rlen_, trace_.p);
     k_ctl<<<1, CTL_THREADS, 0, st_>>>(ctl_.p, partials_.p, n_partials_, g_.ncells, 2 * g_.ncells - 2);
     kernel_launches += 3;

@@ -14,14 +14,13 @@ with gpu.create({k: (None if k in ("name", "bin1", "bin2") else v) for k, v in m
 r = gfl_solve(gpu, n, out['phihat'], out['weight'], 2.5, 1e-12, maxsteps, 0)
 t = np.fromfile("gpurun_out/prox_trace.bin", dtype=np.int64).reshape(-1, 4)
 load, taut, outp = t[:, 0], t[:, 1], t[:, 2]
-smid = (t[:, 3] >> 48); t0 = t[:, 3] & ((1 << 48) - 1)
+smid = (t[:, 3] >> 48); nr = t[:, 3] & ((1 << 48) - 1)
 tot = load + taut + outp
 print("chains", len(t), "sum cycles load/taut/out (M):", load.sum() / 1e6, taut.sum() / 1e6, outp.sum() / 1e6)
 for q in (0, 1, 2, 3, 100, 101, 1000, 1001, 2400, 2401, 4000, 4797):
     L = n - q // 2
-    print(f"q={q} L={L} sm={smid[q]} load={load[q]} taut={taut[q]} out={outp[q]}  taut/L={taut[q]/L:.1f}")
+    print(f"q={q} L={L} sm={smid[q]} load={load[q]} taut={taut[q]} out={outp[q]}  rounds={nr[q]} cycles/round={taut[q]/max(nr[q],1):.0f}")
 print("max chain total", tot.max(), "at q", tot.argmax())
 per_sm = np.bincount(smid, weights=tot)
 print("per-SM summed warp-cycles: min/mean/max", per_sm.min(), per_sm.mean(), per_sm.max(), " /11 warps ->", per_sm.max() / 11)
-span = (t0 + tot).max() - t0.min()
-print("kernel span (first start -> last end, cycles, same-SM clocks only approx):", span)
+print("total rounds", nr.sum(), "mean cycles/round", taut.sum() / nr.sum())
