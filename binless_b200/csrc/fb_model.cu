@@ -5,6 +5,8 @@
 #include <cstdio>
 #include <cstring>
 #include <atomic>
+#include <chrono>
+#include <cstdlib>
 #include <future>
 #include <map>
 #include <thread>
@@ -14,6 +16,16 @@ namespace fb {
 std::string g_last_error;
 
 namespace {
+
+// development aid: FB_TIMING=1 prints host wall-clock per phase of run_signal
+struct PhaseTimer {
+    bool on = std::getenv("FB_TIMING") != nullptr;
+    double acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    std::chrono::steady_clock::time_point t;
+    void start() { if (on) t = std::chrono::steady_clock::now(); }
+    void stop(int k) { if (on) acc[k] += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t).count(); }
+};
+PhaseTimer g_pt;
 
 const char *kSizeMsg = "Input size should be N(N+1)/2 dense matrix of observed counts for each dataset";
 
@@ -243,7 +255,9 @@ void summary_from_sums(int mode, const std::vector<double> &a, const std::vector
 
 void Model::fit_expo(int mode) {
     std::vector<double> a, b, ph, wt;
+    g_pt.start();
     leg_sums(LEG_EXPO, mode, a, b);
+    g_pt.stop(0);
     summary_from_sums(mode, a, b, expo_est_, expo_nobs_, ph, wt);
     expo_est_ = ph; // no centring, no cap (fast_exposure.hpp:63-70)
     upload_tables();
@@ -251,7 +265,9 @@ void Model::fit_expo(int mode) {
 
 void Model::fit_bias(int mode) {
     std::vector<double> a, b, ph, wt;
+    g_pt.start();
     leg_sums(LEG_BIAS, mode, a, b);
+    g_pt.stop(0);
     summary_from_sums(mode, a, b, bias_est_, bias_nobs_, ph, wt);
     // FitterImpl<Leg,Mean>::update_params (fast_fitter_mean.hpp:55-79): centre, then cap at 3 sd
     double num = 0, den = 0;
@@ -268,9 +284,13 @@ void Model::fit_bias(int mode) {
 
 void Model::fit_decay(int mode) {
     std::vector<double> a, b, ph, wt;
+    g_pt.start();
     leg_sums(LEG_DECAY, mode, a, b);
+    g_pt.stop(0);
+    g_pt.start();
     summary_from_sums(mode, a, b, dec_.binned_estimate(), dec_nobs_, ph, wt);
     dec_.fit(ph, wt, dec_nobs_);
+    g_pt.stop(1);
     upload_tables();
 }
 
@@ -315,7 +335,9 @@ void Model::run_signal(const fb_params *p, fb_signal_out *out) {
     const double tol_val = p->tol_val;
     unsigned bg_steps = p->bg_steps;
     phi_.zero(st_); phihat_.zero(st_); wgt_.zero(st_);
+    g_pt.start();
     build_legs(tol_val, p->free_decay);
+    g_pt.stop(3);
     // initial Poisson fits, in this order (fast_binless.cpp:104-115)
     fit_expo(MODE_POISSON);
     fit_decay(MODE_POISSON);
@@ -342,7 +364,9 @@ void Model::run_signal(const fb_params *p, fb_signal_out *out) {
             signal_yw(t_, tables(tab_), alpha_, obs_.p, nobs_.p, phi_.p, 0, phihat_.p, wgt_.p, st_);
             kernel_launches += 1;
             for (int d = 0; d < D; ++d) {
+                g_pt.start();
                 const int steps = flo.optimize(phihat_.p + (size_t)d * nc, wgt_.p + (size_t)d * nc, lam2[d], flo_tol);
+                g_pt.stop(2);
                 ms_solver += flo.ms_last;
                 const int it = steps - 1;
                 if (out->solve_iters && n_solves < out->solve_iters_cap) out->solve_iters[n_solves] = it;
@@ -373,6 +397,11 @@ void Model::run_signal(const fb_params *p, fb_signal_out *out) {
     kernel_launches += flo.kernel_launches;
     if (p->verbose) std::printf("done\n");
     FB_CUDA(cudaEventRecord(ev1_, st_));
+    if (g_pt.on) {
+        std::fprintf(stderr, "[fb timing] leg passes %.2f ms, decay GAM %.2f ms, solves (host wall) %.2f ms (device %.2f), build_legs %.2f ms\n",
+                     g_pt.acc[0], g_pt.acc[1], g_pt.acc[2], ms_solver, g_pt.acc[3]);
+        for (double &a : g_pt.acc) a = 0;
+    }
 
     // get_as_dataframe, Signal overload (fast_dataframe.cpp:9-110)
     {
