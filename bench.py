@@ -40,6 +40,16 @@ ALPHA, LAM2, LAM1 = 0.5, 2.5, 0.0
 ADMM_BYTES_PER_CELL_ITER = 104  # DESIGN.md section 4 / SURVEY.md section 8(d)
 
 
+def ncu_traffic():
+    """DRAM bytes (read + write) of one ADMM iteration from the committed `ncu --set full` capture (profiles/)."""
+    path = os.path.join(ROOT, "profiles", "r1o_admm_iteration_ncu_full_summary.json")
+    try:
+        rows = json.load(open(path))
+        return int(sum((r["dram_read"] + r["dram_write"]) * 1e6 for r in rows))
+    except Exception:
+        return None
+
+
 def measured_peak():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(path):
@@ -208,8 +218,10 @@ def run_cuda(args):
         "gpu_launches": int(launches),
         "clocks": clk,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": None, "peak_source": peak_src,
-                     "kernel": "ADMM iteration of the fused-lasso solve (GflSolver::iteration)",
+                     "traffic": ncu_traffic(), "peak_source": peak_src,
+                     "traffic_source": "ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum of k_beta + k_prox + k_ctl, "
+                                       "one iteration (profiles/r1o_admm_iteration_ncu_full_summary.json)",
+                     "kernel": "ADMM iteration of the fused-lasso solve (GflSolver::iteration = k_beta + k_prox + k_ctl)",
                      "bytes_per_launch": ADMM_BYTES_PER_CELL_ITER * ncells, "us_per_launch": sec_per_iter * 1e6,
                      "solver_share_of_device_time": ms_solver / max(ms_dev, 1e-9)},
     }
