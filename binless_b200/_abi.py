@@ -65,7 +65,7 @@ class fb_gfl_state(C.Structure):
 
 
 ENTRY_POINTS = ["create", "destroy", "last_error", "run_signal", "restore", "run_difference",
-                "eval_cv", "gfl_solve", "set_interrupt_cb", "kernel_launches"]
+                "eval_cv", "gfl_solve", "set_interrupt_cb", "kernel_launches", "release_cached_memory"]
 
 
 def _dp(a):

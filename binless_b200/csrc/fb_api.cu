@@ -59,6 +59,12 @@ FB_API int fb_set_interrupt_cb(fb_handle *h, int (*cb)(void *), void *arg) {
     return FB_OK;
 }
 
+FB_API void fb_release_cached_memory(void) {
+    cudaDeviceSynchronize();
+    fb::BlockCache::device().trim();
+    fb::BlockCache::host().trim();
+}
+
 FB_API int64_t fb_kernel_launches(const fb_handle *h) { return h ? h->m.kernel_launches : 0; }
 
 FB_API int fb_gfl_solve(int nbins, unsigned maxdiag, const double *y, const double *w, double lam2, double converge,

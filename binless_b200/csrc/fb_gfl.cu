@@ -570,13 +570,14 @@ GflSolver::GflSolver(int nbins, unsigned maxdiag, cudaStream_t stream) : nbins_(
     }
     ctl_.alloc(1);
     if (std::getenv("FB_PROX_TRACE")) { trace_.alloc(4 * (size_t)g_.nchains()); trace_.zero(); }
-    FB_CUDA(cudaMallocHost((void **)&h_ctl_, sizeof(GflCtl)));
+    h_ctl_ = static_cast<GflCtl *>(BlockCache::host().get(sizeof(GflCtl)));
     FB_CUDA(cudaEventCreate(&ev0_)); FB_CUDA(cudaEventCreate(&ev1_));
     reset();
 }
 
 GflSolver::~GflSolver() {
-    if (h_ctl_) cudaFreeHost(h_ctl_);
+    cudaStreamSynchronize(st_); // buffers go back to the block cache only when nothing uses them any more
+    if (h_ctl_) BlockCache::host().put(h_ctl_, sizeof(GflCtl));
     cudaEventDestroy(ev0_); cudaEventDestroy(ev1_);
 }
 

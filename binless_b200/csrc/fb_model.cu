@@ -76,6 +76,7 @@ Model::Model(int nbins, const fb_mat *mat) {
 }
 
 Model::~Model() {
+    if (st_) cudaStreamSynchronize(st_); // buffers go back to the block cache only when nothing uses them any more
     if (ev0_) cudaEventDestroy(ev0_);
     if (ev1_) cudaEventDestroy(ev1_);
     if (st_) cudaStreamDestroy(st_);

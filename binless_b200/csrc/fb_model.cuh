@@ -27,8 +27,9 @@ struct PinBuf {
     PinBuf() {}
     PinBuf(const PinBuf &) = delete;
     PinBuf &operator=(const PinBuf &) = delete;
-    ~PinBuf() { if (p) cudaFreeHost(p); }
-    void alloc(size_t n_) { if (p) cudaFreeHost(p); p = nullptr; n = n_; if (n) FB_CUDA(cudaMallocHost((void **)&p, n * sizeof(T))); }
+    ~PinBuf() { release(); }
+    void release() { if (p) BlockCache::host().put(p, n * sizeof(T)); p = nullptr; n = 0; }
+    void alloc(size_t n_) { release(); n = n_; if (n) p = static_cast<T *>(BlockCache::host().get(n * sizeof(T))); }
 };
 
 class Model {

@@ -3,6 +3,9 @@
 #include <cuda_runtime.h>
 #include <cstdint>
 #include <cstdio>
+#include <exception>
+#include <map>
+#include <mutex>
 #include <stdexcept>
 #include <string>
 
@@ -24,6 +27,53 @@ struct Interrupted : std::runtime_error { using std::runtime_error::runtime_erro
 
 #define FB_LAUNCH_CHECK() FB_CUDA(cudaGetLastError())
 
+// Size-keyed cache of device / pinned allocations: fast_binless is called repeatedly with same-shaped inputs (one
+// call per locus, then fast_binless_difference on the result), and cudaMalloc / cudaFree / cudaMallocHost cost
+// milliseconds each. Blocks are returned to the cache only by owners that have synchronised their stream
+// (every API call of this library ends synchronised), so a cached block is never still in use.
+class BlockCache {
+public:
+    explicit BlockCache(bool pinned) : pinned_(pinned) {}
+    void *get(size_t bytes) {
+        bytes = (bytes + 255) & ~size_t(255);
+        {
+            std::lock_guard<std::mutex> g(mu_);
+            auto it = free_.find(bytes);
+            if (it != free_.end()) { void *p = it->second; free_.erase(it); cached_ -= bytes; return p; }
+        }
+        void *p = nullptr;
+        cudaError_t e = pinned_ ? cudaMallocHost(&p, bytes) : cudaMalloc(&p, bytes);
+        if (e != cudaSuccess) { // give the cached blocks back and retry once
+            cudaGetLastError();
+            trim();
+            e = pinned_ ? cudaMallocHost(&p, bytes) : cudaMalloc(&p, bytes);
+        }
+        if (e != cudaSuccess)
+            throw CudaError(std::string(pinned_ ? "cudaMallocHost" : "cudaMalloc") + " of " + std::to_string(bytes) + " bytes failed: " + cudaGetErrorString(e));
+        return p;
+    }
+    void put(void *p, size_t bytes) {
+        if (!p) return;
+        bytes = (bytes + 255) & ~size_t(255);
+        std::lock_guard<std::mutex> g(mu_);
+        if (cached_ + bytes > limit_) { if (pinned_) cudaFreeHost(p); else cudaFree(p); return; }
+        free_.emplace(bytes, p); cached_ += bytes;
+    }
+    void trim() {
+        std::lock_guard<std::mutex> g(mu_);
+        for (auto &kv : free_) { if (pinned_) cudaFreeHost(kv.second); else cudaFree(kv.second); }
+        free_.clear(); cached_ = 0;
+    }
+    static BlockCache &device() { static BlockCache c(false); return c; }
+    static BlockCache &host() { static BlockCache c(true); return c; }
+private:
+    bool pinned_;
+    std::mutex mu_;
+    std::multimap<size_t, void *> free_;
+    size_t cached_ = 0;
+    size_t limit_ = pinned_ ? (size_t(1) << 30) : (size_t(48) << 30);
+};
+
 // RAII device buffer
 template <typename T>
 struct DevBuf {
@@ -39,9 +89,15 @@ struct DevBuf {
     void alloc(size_t n_) {
         release();
         n = n_;
-        if (n) FB_CUDA(cudaMalloc((void **)&p, n * sizeof(T)));
+        if (n) p = static_cast<T *>(BlockCache::device().get(n * sizeof(T)));
     }
-    void release() { if (p) cudaFree(p); p = nullptr; n = 0; }
+    void release() {
+        if (p) {
+            if (std::uncaught_exceptions()) cudaDeviceSynchronize(); // error unwinding: work may still be queued
+            BlockCache::device().put(p, n * sizeof(T));
+        }
+        p = nullptr; n = 0;
+    }
     void zero(cudaStream_t s = 0) { if (n) FB_CUDA(cudaMemsetAsync(p, 0, n * sizeof(T), s)); }
     void upload(const T *h, size_t cnt, cudaStream_t s = 0) { FB_CUDA(cudaMemcpyAsync(p, h, cnt * sizeof(T), cudaMemcpyHostToDevice, s)); }
     void download(T *h, size_t cnt, cudaStream_t s = 0) const { FB_CUDA(cudaMemcpyAsync(h, p, cnt * sizeof(T), cudaMemcpyDeviceToHost, s)); }

@@ -174,6 +174,10 @@ FB_API int FB_NAME(gfl_solve)(int nbins, unsigned maxdiag, const double *y, cons
                               double lam2, double converge, int maxsteps, int warm,
                               fb_gfl_state *st, double *beta_full);
 
+/* Device and pinned-host blocks of destroyed handles are kept in a size-keyed cache (cudaMalloc / cudaFree cost
+ * milliseconds per call and fast_binless is called once per locus); this returns them to the driver. */
+FB_API void FB_NAME(release_cached_memory)(void);
+
 FB_API int FB_NAME(set_interrupt_cb)(fb_handle *h, int (*cb)(void *), void *arg);
 
 /* Diagnostics: number of CUDA kernels launched by the last run_* / eval_cv call on this handle

@@ -1196,6 +1196,7 @@ FB_API int fbo_eval_cv(fb_handle *h, const fb_params *p, int nlam, const double 
     ORACLE_TRY(h, eval_cv(h->m, p, nlam, lam2, group, outs))
 }
 FB_API int64_t fbo_kernel_launches(const fb_handle *) { return 0; }
+FB_API void fbo_release_cached_memory(void) {}
 FB_API int fbo_set_interrupt_cb(fb_handle *h, int (*cb)(void *), void *arg) { h->m.interrupt_cb = cb; h->m.interrupt_arg = arg; return FB_OK; }
 
 FB_API int fbo_gfl_solve(int nbins, unsigned maxdiag, const double *y, const double *w, double lam2,
