@@ -60,12 +60,17 @@ class fb_cv_out(C.Structure):
                 ("log_signal", c_dp), ("patchno", c_ip)]
 
 
+class fb_sweep_out(C.Structure):
+    _fields_ = [("bic", c_dp), ("chisq", c_dp), ("dof", c_ip), ("steps", c_ip), ("ms_solver", C.c_double),
+                ("admm_cell_iters", C.c_int64)]
+
+
 class fb_gfl_state(C.Structure):
     _fields_ = [("beta", c_dp), ("z", c_dp), ("u", c_dp), ("alpha", C.c_double), ("steps", C.c_int)]
 
 
 ENTRY_POINTS = ["create", "destroy", "last_error", "run_signal", "restore", "run_difference",
-                "eval_cv", "gfl_solve", "set_interrupt_cb", "kernel_launches", "release_cached_memory"]
+                "eval_cv", "sweep_lambda", "gfl_solve", "set_interrupt_cb", "kernel_launches", "release_cached_memory"]
 
 
 def _dp(a):
@@ -121,6 +126,9 @@ class FastBinlessLib:
         self._eval_cv = f("eval_cv")
         self._eval_cv.argtypes = [C.c_void_p, C.POINTER(fb_params), C.c_int, c_dp, C.c_uint, C.POINTER(fb_cv_out)]
         self._eval_cv.restype = C.c_int
+        self._sweep_lambda = f("sweep_lambda")
+        self._sweep_lambda.argtypes = [C.c_void_p, C.POINTER(fb_params), C.c_int, c_dp, C.POINTER(fb_sweep_out)]
+        self._sweep_lambda.restype = C.c_int
         self._kernel_launches = f("kernel_launches")
         self._kernel_launches.argtypes = [C.c_void_p]; self._kernel_launches.restype = C.c_int64
         self._gfl_solve = f("gfl_solve")
@@ -269,6 +277,19 @@ class Handle:
         rc = self.lib._eval_cv(self.h, C.byref(p), lam2a.size, _dp(lam2a), int(group), outs)
         self.lib._check(rc, self.h)
         return keep
+
+    def sweep_lambda(self, alpha, lam2, lam1=0.0, tol_val=0.2, maxdiag=0):
+        """lambda2 / BIC sweep (fb_sweep_lambda): arrays of shape (len(lam2), ndatasets)."""
+        lam2a = _f64(np.atleast_1d(lam2))
+        p = self.lib._params(alpha, lam2a[:1] if lam2a.size else [0.0], lam1, tol_val=tol_val, maxdiag=maxdiag)
+        shape = (lam2a.size, self.ndatasets)
+        bic = np.empty(shape); chisq = np.empty(shape)
+        dof = np.empty(shape, dtype=np.int32); steps = np.empty(shape, dtype=np.int32)
+        o = fb_sweep_out(bic=_dp(bic), chisq=_dp(chisq), dof=_ip(dof), steps=_ip(steps))
+        rc = self.lib._sweep_lambda(self.h, C.byref(p), lam2a.size, _dp(lam2a), C.byref(o))
+        self.lib._check(rc, self.h)
+        return {"lam2": lam2a, "bic": bic, "chisq": chisq, "dof": dof, "steps": steps, "ms_solver": o.ms_solver,
+                "admm_cell_iters": int(o.admm_cell_iters)}
 
 
 def gfl_solve(lib: FastBinlessLib, nbins, y, w, lam2, converge, maxsteps=30000, maxdiag=0, state=None):

@@ -53,6 +53,11 @@ FB_API int fb_eval_cv(fb_handle *h, const fb_params *p, int nlam, const double *
     return guarded(h->m.err, [&] { h->m.eval_cv(p, nlam, lam2, group, outs); });
 }
 
+FB_API int fb_sweep_lambda(fb_handle *h, const fb_params *p, int nlam, const double *lam2, fb_sweep_out *out) {
+    if (!h) { fb::g_last_error = "null handle"; return FB_ERR_ARG; }
+    return guarded(h->m.err, [&] { h->m.sweep_lambda(p, nlam, lam2, out); });
+}
+
 FB_API int fb_set_interrupt_cb(fb_handle *h, int (*cb)(void *), void *arg) {
     if (!h) return FB_ERR_ARG;
     h->m.interrupt_cb = cb; h->m.interrupt_arg = arg;

@@ -657,6 +657,47 @@ void patch_labels(int n, double tol, const double *value, int32_t *parent, int32
     FB_LAUNCH_CHECK();
 }
 
+namespace {
+// chisq partial sums (fixed grid => same bits on every run) and per-patch selection flags
+__global__ void __launch_bounds__(256)
+k_sweep_score(int64_t ncells, const double *__restrict__ phihat, const double *__restrict__ w, const double *__restrict__ beta,
+              const int32_t *__restrict__ labels, double lam1, double half_tol, int32_t *__restrict__ flags,
+              double *__restrict__ partial) {
+    __shared__ double s[32];
+    double acc = 0.0;
+    const int64_t per = (ncells + gridDim.x - 1) / gridDim.x;
+    const int64_t lo = per * blockIdx.x, hi = lo + per < ncells ? lo + per : ncells;
+    for (int64_t i = lo + threadIdx.x; i < hi; i += blockDim.x) {
+        const double b = beta[i];
+        const double soft = b > 0 ? fmax(0., b - lam1) : fmin(0., b + lam1); // soft_threshold(beta, 0, lam1), util.cpp:8-18
+        const double d = phihat[i] - soft;
+        acc += w[i] * (d * d) + lam1 * lam1;
+        if (fabs(soft) > half_tol) flags[labels[i]] = 1;
+    }
+    const double r = block_sum(acc, s);
+    if (threadIdx.x == 0) partial[blockIdx.x] = r;
+}
+__global__ void __launch_bounds__(1024)
+k_sweep_fin(int nblocks, const double *__restrict__ partial, int64_t ncells, const int32_t *__restrict__ flags,
+            double *__restrict__ out2) {
+    __shared__ double s[32];
+    double a = 0.0, c = 0.0;
+    for (int k = threadIdx.x; k < nblocks; k += blockDim.x) a += partial[k];
+    for (int64_t i = threadIdx.x; i < ncells; i += blockDim.x) c += flags[i] ? 1.0 : 0.0;
+    const double ra = block_sum(a, s);
+    const double rc = block_sum(c, s);
+    if (threadIdx.x == 0) { out2[0] = ra; out2[1] = rc; }
+}
+} // namespace
+
+void sweep_score(int64_t ncells, const double *phihat, const double *w, const double *beta, const int32_t *labels,
+                 double lam1, double tol, int32_t *flags, double *partial, double *out2, cudaStream_t st) {
+    FB_CUDA(cudaMemsetAsync(flags, 0, ncells * sizeof(int32_t), st));
+    k_sweep_score<<<SWEEP_BLOCKS, 256, 0, st>>>(ncells, phihat, w, beta, labels, lam1, tol / 2, flags, partial);
+    k_sweep_fin<<<1, 1024, 0, st>>>(SWEEP_BLOCKS, partial, ncells, flags, out2);
+    FB_LAUNCH_CHECK();
+}
+
 void fill_i32(int32_t *p, int64_t n, int32_t v, cudaStream_t st) {
     k_fill_i32<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(p, n, v);
     FB_LAUNCH_CHECK();

@@ -90,4 +90,10 @@ void diff_finish(const Tri &t, int ref0, const double *phihat, const double *w, 
 void patch_labels(int n, double tol, const double *value, int32_t *parent, int32_t *scan, int32_t *labels, cudaStream_t st);
 void fill_i32(int32_t *p, int64_t n, int32_t v, cudaStream_t st);
 
+// BIC pieces of one (lambda2, dataset) point of the sweep: out2 = {chisq, dof} (device doubles).
+// flags: ncells int32 scratch, partial: SWEEP_BLOCKS doubles scratch.
+constexpr int SWEEP_BLOCKS = 1024;
+void sweep_score(int64_t ncells, const double *phihat, const double *w, const double *beta, const int32_t *labels,
+                 double lam1, double tol, int32_t *flags, double *partial, double *out2, cudaStream_t st);
+
 } // namespace fb

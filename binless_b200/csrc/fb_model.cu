@@ -550,4 +550,51 @@ void Model::eval_cv(const fb_params *p, int nlam, const double *lam2v, unsigned 
     kernel_launches += flo.kernel_launches;
 }
 
+// ---------------------------------------------------------------------------------------------
+// lambda2 / BIC sweep (fastbinless.h: fb_sweep_lambda)
+// ---------------------------------------------------------------------------------------------
+void Model::sweep_lambda(const fb_params *p, int nlam, const double *lam2v, fb_sweep_out *out) {
+    if (!p || !out || !lam2v || nlam < 0) throw ArgError("null argument");
+    if (!has_state_) throw StateError("sweep_lambda needs a fitted or restored model");
+    const int n = t_.n, D = t_.D;
+    const int64_t nc = t_.ncells, N = t_.N();
+    alpha_ = p->alpha;
+    kernel_launches = 0;
+    const std::vector<double> lam1 = broadcast(p->lam1, p->n_lam1, D);
+    DevBuf<double> y(N), w(N), beta(nc), partial(SWEEP_BLOCKS), res(2);
+    DevBuf<int32_t> parent(nc), scan(nc + nc / 4096 + 8), labels(nc), flags(nc);
+    PinBuf<double> res_h; res_h.alloc(2);
+    signal_yw(t_, tables(tab_), alpha_, obs_.p, nobs_.p, phi_.p, 0, y.p, w.p, st_);
+    kernel_launches += 1;
+    GflSolver flo(n, p->maxdiag, st_);
+    double ms_solver = 0;
+    int64_t cell_iters = 0;
+    for (int k = 0; k < nlam; ++k) {
+        check_interrupt();
+        for (int d = 0; d < D; ++d) {
+            flo.reset();                                   // cold start: the points are independent of each other
+            const int steps = flo.optimize(y.p + (size_t)d * nc, w.p + (size_t)d * nc, lam2v[k], p->tol_val / 20.);
+            ms_solver += flo.ms_last;
+            cell_iters += (int64_t)(steps - 1) * flo.grid().ncells;
+            flo.get_beta_full(beta.p);
+            center_dataset(nc, nobs_.p + (size_t)d * nc, beta.p, scratch_.p + 16, st_);
+            patch_labels(n, p->tol_val, beta.p, parent.p, scan.p, labels.p, st_);
+            sweep_score(nc, y.p + (size_t)d * nc, w.p + (size_t)d * nc, beta.p, labels.p, lam1[d], p->tol_val, flags.p,
+                        partial.p, res.p, st_);
+            kernel_launches += 3 + 6 + 2;
+            FB_CUDA(cudaMemcpyAsync(res_h.p, res.p, 2 * sizeof(double), cudaMemcpyDeviceToHost, st_));
+            FB_CUDA(cudaStreamSynchronize(st_));
+            const size_t o = (size_t)k * D + d;
+            const double chisq = res_h.p[0];
+            const int dof = (int)res_h.p[1];
+            if (out->chisq) out->chisq[o] = chisq;
+            if (out->dof) out->dof[o] = dof;
+            if (out->steps) out->steps[o] = steps;
+            if (out->bic) out->bic[o] = chisq + std::log(expo_nobs_[d]) * dof; // ScoreAssembler<BIC>: lsnc = log(sum nobs)
+        }
+    }
+    kernel_launches += flo.kernel_launches;
+    out->ms_solver = ms_solver; out->admm_cell_iters = cell_iters;
+}
+
 } // namespace fb

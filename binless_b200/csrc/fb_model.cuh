@@ -41,6 +41,7 @@ public:
                  const fb_mean_state *exposures);
     void run_difference(int ref, const fb_params *p, fb_diff_out *out);
     void eval_cv(const fb_params *p, int nlam, const double *lam2, unsigned group, fb_cv_out *outs);
+    void sweep_lambda(const fb_params *p, int nlam, const double *lam2, fb_sweep_out *out);
 
     std::string err;
     int (*interrupt_cb)(void *) = nullptr;

@@ -157,6 +157,24 @@ FB_API int FB_NAME(run_difference)(fb_handle *h, int ref, const fb_params *p, fb
 FB_API int FB_NAME(eval_cv)(fb_handle *h, const fb_params *p, int nlam, const double *lam2,
                             unsigned group, fb_cv_out *outs);
 
+/* lambda2 / BIC sweep on a fitted or restored model (BASELINE.json config 3): for every lambda2 value and every
+ * dataset one COLD-START fused-lasso solve of the signal step (fresh FusedLassoGaussianEstimator, alpha = 5, as
+ * ScorePreparator<BIC> does per candidate: ScorePreparator.ipp:53-64), the solution centred like step_signal
+ * (fast_binless.ipp:33-44), and the BIC of the optimized path evaluated on the fast path's IRLS quantities:
+ *   chisq = sum_cells [ w (phihat - soft(beta, lam1))^2 + lam1^2 ]     Likelihoods.hpp:25-42 (eCprime = 0)
+ *   dof   = number of patches (get_patch_numbers at tol_val on beta) holding a cell with |soft(beta, lam1)| > tol_val/2
+ *                                                                      DOFComputer.hpp:16-24
+ *   bic   = chisq + log(sum nobs of the dataset) * dof                 ScoreAssembler.hpp:41-55
+ * The points are independent of each other, so a caller shards the lambda2 list over processes / GPUs.
+ * Arrays hold nlam * ndatasets entries, lambda-major; any pointer may be NULL. */
+typedef struct {
+    double *bic, *chisq;
+    int32_t *dof, *steps;        /* steps = return value of graph_fused_lasso_weight_warm per solve */
+    double ms_solver;
+    int64_t admm_cell_iters;
+} fb_sweep_out;
+FB_API int FB_NAME(sweep_lambda)(fb_handle *h, const fb_params *p, int nlam, const double *lam2, fb_sweep_out *out);
+
 /* Stand-alone fused-lasso solve on the triangle grid (the
  * FusedLassoGaussianEstimator<GFLLibrary> object of the reference,
  * FusedLassoGaussianEstimator.hpp:16-71, GFLLibraryTriangleImpl.cpp:60-71).

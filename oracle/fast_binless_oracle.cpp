@@ -1160,6 +1160,53 @@ void eval_cv(Model &m, const fb_params *p, int nlam, const double *lam2v, unsign
     d.beta = signal_ori;
 }
 
+/* lambda2 / BIC sweep (fastbinless.h: sweep_lambda): cold-start solve per (lambda2, dataset); chi square of
+ * Likelihoods.hpp:25-42 with eCprime = 0, dof of DOFComputer.hpp:16-24, BIC of ScoreAssembler.hpp:41-55 */
+void sweep_lambda(Model &m, const fb_params *p, int nlam, const double *lam2v, fb_sweep_out *out) {
+    Data &d = m.d;
+    if (!m.has_state) throw std::logic_error("sweep_lambda needs a fitted or restored model");
+    m.alpha = p->alpha;
+    const vec lam1 = broadcast(p->lam1, p->n_lam1, d.ndatasets);
+    vec res, wts;
+    m.residuals(d.beta, res, wts);
+    vec phihat(d.N);
+    for (unsigned i = 0; i < d.N; ++i) phihat[i] = res[i] + d.beta[i];
+    double ms = 0; int64_t cell_iters = 0;
+    std::vector<int32_t> patch(d.ncells);
+    for (int k = 0; k < nlam; ++k)
+        for (unsigned ds = 0; ds < d.ndatasets; ++ds) {
+            const size_t off = (size_t)ds * d.ncells;
+            GflSolver flo(d.nbins, p->maxdiag);
+            vec y(phihat.begin() + off, phihat.begin() + off + d.ncells), wt(wts.begin() + off, wts.begin() + off + d.ncells);
+            double t0 = now_ms();
+            flo.optimize(y, wt, lam2v[k], p->tol_val / 20.);
+            ms += now_ms() - t0;
+            cell_iters += (int64_t)(flo.last_steps - 1) * flo.N;
+            vec beta = flo.get();
+            double avg = 0, wsum = 0;
+            for (unsigned i = 0; i < d.ncells; ++i) { int no = d.nobs[off + i]; avg += beta[i] * no; wsum += no; }
+            avg = avg / wsum;
+            for (unsigned i = 0; i < d.ncells; ++i) beta[i] = beta[i] - avg;
+            patch_numbers(d.nbins, p->tol_val, beta.data(), patch.data());
+            double chisq = 0;
+            std::vector<char> sel(d.ncells, 0);
+            for (unsigned i = 0; i < d.ncells; ++i) {
+                const double b = beta[i], l1 = lam1[ds];
+                const double soft = (b > 0) ? std::max(0., b - l1) : std::min(0., b + l1);
+                chisq += wt[i] * (y[i] - soft) * (y[i] - soft) + l1 * l1;
+                if (std::fabs(soft) > p->tol_val / 2) sel[patch[i]] = 1;
+            }
+            int dof = 0;
+            for (char c : sel) dof += c;
+            const size_t o = (size_t)k * d.ndatasets + ds;
+            if (out->chisq) out->chisq[o] = chisq;
+            if (out->dof) out->dof[o] = dof;
+            if (out->steps) out->steps[o] = flo.last_steps;
+            if (out->bic) out->bic[o] = chisq + std::log(wsum) * dof;
+        }
+    out->ms_solver = ms; out->admm_cell_iters = cell_iters;
+}
+
 } // namespace
 
 struct fb_handle { Model m; };
@@ -1194,6 +1241,9 @@ FB_API int fbo_restore(fb_handle *h, const double *log_signal, const fb_mean_sta
 FB_API int fbo_run_difference(fb_handle *h, int ref, const fb_params *p, fb_diff_out *out) { ORACLE_TRY(h, run_difference(h->m, ref, p, out)) }
 FB_API int fbo_eval_cv(fb_handle *h, const fb_params *p, int nlam, const double *lam2, unsigned group, fb_cv_out *outs) {
     ORACLE_TRY(h, eval_cv(h->m, p, nlam, lam2, group, outs))
+}
+FB_API int fbo_sweep_lambda(fb_handle *h, const fb_params *p, int nlam, const double *lam2, fb_sweep_out *out) {
+    ORACLE_TRY(h, sweep_lambda(h->m, p, nlam, lam2, out))
 }
 FB_API int64_t fbo_kernel_launches(const fb_handle *) { return 0; }
 FB_API void fbo_release_cached_memory(void) {}

@@ -247,3 +247,30 @@ def test_full_size_c2_matches_oracle(gpu_lib, oracle):
     with oracle.create(mat, n) as ho:
         oo = ho.run_signal(0.5, 2.5, 0.0)
     compare_signal(og, oo)
+
+
+def test_sweep_lambda_matches_oracle(gpu_lib, oracle):
+    """fb_sweep_lambda (config 3): cold-start solve + BIC per (lambda2, dataset); dof and step counts exact."""
+    n, D = 64, 2
+    mat = synth(n, D, 5000, 11)
+    lams = 10.0 ** np.linspace(-1, 2, 7)
+    with oracle.create(mat, n) as ho:
+        fit = ho.run_signal(0.5, 2.5, 0.0)
+        ro = ho.sweep_lambda(0.5, lams, [0.05, 0.1], tol_val=0.2)
+    with gpu_lib.create(mat, n) as hg:
+        hg.restore(fit["log_signal"], fit["biases"], fit["decay"], fit["exposures"])
+        rg = hg.sweep_lambda(0.5, lams, [0.05, 0.1], tol_val=0.2)
+        assert hg.kernel_launches() > 0
+    assert np.array_equal(rg["steps"], ro["steps"])
+    assert np.array_equal(rg["dof"], ro["dof"])
+    assert np.allclose(rg["chisq"], ro["chisq"], rtol=1e-9, atol=0)
+    assert np.allclose(rg["bic"], ro["bic"], rtol=1e-9, atol=0)
+    # band variant
+    with oracle.create(mat, n) as ho:
+        ho.restore(fit["log_signal"], fit["biases"], fit["decay"], fit["exposures"])
+        ro = ho.sweep_lambda(0.5, lams[:3], 0.0, tol_val=0.2, maxdiag=20)
+    with gpu_lib.create(mat, n) as hg:
+        hg.restore(fit["log_signal"], fit["biases"], fit["decay"], fit["exposures"])
+        rg = hg.sweep_lambda(0.5, lams[:3], 0.0, tol_val=0.2, maxdiag=20)
+    assert np.array_equal(rg["steps"], ro["steps"]) and np.array_equal(rg["dof"], ro["dof"])
+    assert np.allclose(rg["bic"], ro["bic"], rtol=1e-9, atol=0)
