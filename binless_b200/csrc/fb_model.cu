@@ -55,6 +55,37 @@ std::vector<double> broadcast(const double *p, int np, int n) {
     return std::vector<double>(n, p[0]);
 }
 
+// csvfile of the reference (csvfile.hpp:30-117, USE_BOOST = 0): quoted header, then one row per cell with every value
+// printed as std::fixed << std::setprecision(4), comma separated (fast_dataframe.cpp:23-57). Rows are formatted by
+// several host threads, slab by slab, and written in order.
+void write_signal_csv(const char *path, int64_t N, const double *const cols[7]) {
+    FILE *f = std::fopen(path, "w");
+    if (!f) { std::printf("Exception creating csv file: cannot open %s\n", path); return; } // the reference only reports it
+    std::fputs("\"phihat\",\"weight\",\"biasmat\",\"decaymat\",\"signal\",\"binless\",\"background\"\n", f);
+    const int nthr = (int)std::min(16u, std::max(1u, std::thread::hardware_concurrency()));
+    const int64_t slab = 1 << 20;
+    std::vector<std::string> parts(nthr);
+    for (int64_t base = 0; base < N; base += slab) {
+        const int64_t cnt = std::min<int64_t>(slab, N - base);
+        std::vector<std::future<void>> fut;
+        for (int t = 0; t < nthr; ++t)
+            fut.push_back(std::async(std::launch::async, [&, t] {
+                const int64_t lo = base + cnt * t / nthr, hi = base + cnt * (t + 1) / nthr;
+                std::string &o = parts[t];
+                o.clear(); o.reserve((size_t)(hi - lo) * 64);
+                char buf[512];
+                for (int64_t i = lo; i < hi; ++i) {
+                    const int len = std::snprintf(buf, sizeof buf, "%.4f,%.4f,%.4f,%.4f,%.4f,%.4f,%.4f\n", cols[0][i], cols[1][i],
+                                                  cols[2][i], cols[3][i], cols[4][i], cols[5][i], cols[6][i]);
+                    o.append(buf, (size_t)std::min<int>(len, (int)sizeof buf - 1));
+                }
+            }));
+        for (auto &x : fut) x.get();
+        for (int t = 0; t < nthr; ++t) std::fwrite(parts[t].data(), 1, parts[t].size(), f);
+    }
+    std::fclose(f);
+}
+
 int host_threads() {
     unsigned h = std::thread::hardware_concurrency();
     return (int)std::min(16u, std::max(1u, h));
@@ -408,14 +439,15 @@ void Model::run_signal(const fb_params *p, fb_signal_out *out) {
     {
         DevBuf<double> lam1_d(D), cols;
         lam1_d.upload(lam1.data(), D, st_);
+        const bool csv = p->csv_out && p->csv_out[0];
         double *want[5] = {out->background, out->biasmat, out->decaymat, out->signal, out->binless};
         int nwant = 0;
-        for (double *w : want) nwant += (w != nullptr);
+        for (double *w : want) nwant += (w != nullptr || csv);
         double *dcol[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
         if (nwant) {
             cols.alloc((size_t)nwant * N);
             int k = 0;
-            for (int c = 0; c < 5; ++c) if (want[c]) dcol[c] = cols.p + (size_t)(k++) * N;
+            for (int c = 0; c < 5; ++c) if (want[c] || csv) dcol[c] = cols.p + (size_t)(k++) * N;
             output_signal(t_, tables(tab_), nobs_.p, phi_.p, lam1_d.p, dcol[0], dcol[1], dcol[2], dcol[3], dcol[4], st_);
             kernel_launches += 1;
             for (int c = 0; c < 5; ++c) download(want[c], dcol[c], N);
@@ -424,9 +456,19 @@ void Model::run_signal(const fb_params *p, fb_signal_out *out) {
         download(out->weight, wgt_.p, N);
         download(out->log_signal, phi_.p, N);
         FB_CUDA(cudaStreamSynchronize(st_));
+        if (csv) { // fast_dataframe.cpp:23-57: phihat, weight, biasmat, decaymat, signal, binless, background
+            std::vector<double> hbuf((size_t)7 * N);
+            const double *src[7] = {phihat_.p, wgt_.p, dcol[1], dcol[2], dcol[3], dcol[4], dcol[0]};
+            const double *hc[7];
+            for (int c = 0; c < 7; ++c) {
+                FB_CUDA(cudaMemcpyAsync(hbuf.data() + (size_t)c * N, src[c], N * sizeof(double), cudaMemcpyDeviceToHost, st_));
+                hc[c] = hbuf.data() + (size_t)c * N;
+            }
+            FB_CUDA(cudaStreamSynchronize(st_));
+            write_signal_csv(p->csv_out, N, hc);
+        }
     }
     patchnos(phi_.p, tol_val, p->compute_patchnos != 0, out->patchno);
-    if (p->csv_out && p->csv_out[0]) throw ArgError("csv_out is not supported by the CUDA library yet");
     // leg states (fast_binless.cpp:179-183)
     if (out->biases.estimate) std::memcpy(out->biases.estimate, bias_est_.data(), bias_est_.size() * sizeof(double));
     out->biases.n = nb_bias_; out->biases.mean = 0;

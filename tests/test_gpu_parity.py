@@ -274,3 +274,22 @@ def test_sweep_lambda_matches_oracle(gpu_lib, oracle):
         rg = hg.sweep_lambda(0.5, lams[:3], 0.0, tol_val=0.2, maxdiag=20)
     assert np.array_equal(rg["steps"], ro["steps"]) and np.array_equal(rg["dof"], ro["dof"])
     assert np.allclose(rg["bic"], ro["bic"], rtol=1e-9, atol=0)
+
+
+def test_csv_out_matches_oracle(gpu_lib, oracle, tmp_path):
+    """csv_out (fast_dataframe.cpp:23-57, csvfile.hpp with USE_BOOST = 0): quoted header + one "%.4f" row per cell."""
+    n, D = 33, 2
+    mat = synth(n, D, 5000, 3)
+    fg, fo = str(tmp_path / "gpu.csv"), str(tmp_path / "cpu.csv")
+    with gpu_lib.create(mat, n) as hg:
+        hg.run_signal(0.49, [2.53, 4.51], [0.13, 0.10], csv_out=fg)
+    with oracle.create(mat, n) as ho:
+        ho.run_signal(0.49, [2.53, 4.51], [0.13, 0.10], csv_out=fo)
+    lg, lo = open(fg).read().splitlines(), open(fo).read().splitlines()
+    assert lg[0] == lo[0] == '"phihat","weight","biasmat","decaymat","signal","binless","background"'
+    assert len(lg) == len(lo) == 1 + D * n * (n + 1) // 2
+    a = np.array([[float(x) for x in l.split(",")] for l in lg[1:]])
+    b = np.array([[float(x) for x in l.split(",")] for l in lo[1:]])
+    assert np.abs(a - b).max() <= 1.0001e-4            # 4 printed decimals: at most one unit in the last place
+    assert np.mean(np.array(lg[1:]) == np.array(lo[1:])) > 0.999
+    assert all(len(l.split(",")) == 7 and all(len(x.split(".")[1]) == 4 for x in l.split(",")) for l in lg[1:50])
