@@ -70,7 +70,8 @@ class fb_gfl_state(C.Structure):
 
 
 ENTRY_POINTS = ["create", "destroy", "last_error", "run_signal", "restore", "run_difference",
-                "eval_cv", "sweep_lambda", "gfl_solve", "set_interrupt_cb", "kernel_launches", "release_cached_memory"]
+                "eval_cv", "sweep_lambda", "gfl_solve", "set_interrupt_cb", "kernel_launches", "release_cached_memory",
+                "comm_unique_id", "comm_init", "comm_destroy", "comm_rank", "comm_world", "shard_plan"]
 
 
 def _dp(a):
@@ -135,6 +136,30 @@ class FastBinlessLib:
         self._gfl_solve.argtypes = [C.c_int, C.c_uint, c_dp, c_dp, C.c_double, C.c_double, C.c_int, C.c_int,
                                     C.POINTER(fb_gfl_state), c_dp]
         self._gfl_solve.restype = C.c_int
+        self._comm_unique_id = f("comm_unique_id"); self._comm_unique_id.argtypes = [C.c_void_p]; self._comm_unique_id.restype = C.c_int
+        self._comm_init = f("comm_init"); self._comm_init.argtypes = [C.c_int, C.c_int, C.c_void_p]; self._comm_init.restype = C.c_int
+        self._comm_destroy = f("comm_destroy"); self._comm_destroy.argtypes = []; self._comm_destroy.restype = C.c_int
+        self._shard_plan = f("shard_plan")
+        self._shard_plan.argtypes = [C.c_int, C.c_uint, C.c_int, c_ip, c_ip]; self._shard_plan.restype = C.c_int
+
+    # ---- multi-GPU (one process per GPU) --------------------------------
+    def shard_plan(self, nbins, world, maxdiag=0):
+        """(row_begin, col_begin): the equal-cell row / column blocks of the trail-block sharding (host only)."""
+        rb = np.zeros(world + 1, dtype=np.int32); cb = np.zeros(world + 1, dtype=np.int32)
+        self._check(self._shard_plan(int(nbins), int(maxdiag), int(world), _ip(rb), _ip(cb)), None)
+        return rb, cb
+
+    def comm_unique_id(self) -> bytes:
+        buf = C.create_string_buffer(128)
+        self._check(self._comm_unique_id(buf), None)
+        return buf.raw
+
+    def comm_init(self, rank, world, uid: bytes = b""):
+        buf = C.create_string_buffer(uid, 128) if uid else None
+        self._check(self._comm_init(int(rank), int(world), buf), None)
+
+    def comm_destroy(self):
+        self._check(self._comm_destroy(), None)
 
     # ---- helpers -------------------------------------------------------
     def _check(self, rc, h=None):

@@ -2,6 +2,7 @@
 // exception -> status translation, nothing else. The Rcpp shim (r/fastbinless_shim.cpp) and the ctypes
 // mirror (binless_b200/_abi.py) bind exactly these symbols.
 #include "fb_model.cuh"
+#include "fb_comm.cuh"
 #include <string>
 
 struct fb_handle { fb::Model m; fb_handle(int nbins, const fb_mat *mat) : m(nbins, mat) {} };
@@ -15,6 +16,7 @@ int guarded(std::string &err, F &&f) {
     catch (const fb::StateError &e) { err = e.what(); return FB_ERR_STATE; }
     catch (const fb::NumError &e) { err = e.what(); return FB_ERR_NUMERIC; }
     catch (const fb::Interrupted &e) { err = e.what(); return FB_ERR_INTERRUPT; }
+    catch (const fb::CommError &e) { err = e.what(); return FB_ERR_COMM; }
     catch (const std::bad_alloc &) { err = "out of host memory"; return FB_ERR_ARG; }
     catch (const std::exception &e) { err = e.what(); return FB_ERR_NUMERIC; }
 }
@@ -94,6 +96,32 @@ FB_API int fb_gfl_solve(int nbins, unsigned maxdiag, const double *y, const doub
             dout.download(beta_full, nc);
             FB_CUDA(cudaDeviceSynchronize());
         }
+    });
+}
+
+// ---- one process per GPU: trail-block sharding of the fused-lasso solve over the ranks of one NCCL communicator ----
+FB_API int fb_comm_unique_id(void *id128) {
+    if (!id128) { fb::g_last_error = "null argument"; return FB_ERR_ARG; }
+    return guarded(fb::g_last_error, [&] { fb::Comm::get().unique_id(id128); });
+}
+FB_API int fb_comm_init(int rank, int world, const void *id128) {
+    if (world > 1 && !id128) { fb::g_last_error = "null argument"; return FB_ERR_ARG; }
+    return guarded(fb::g_last_error, [&] {
+        int ndev = 0;
+        if (world > 1 && (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0))
+            throw fb::CudaError("no CUDA device available (there is no CPU fallback)");
+        fb::Comm::get().init(rank, world, id128);
+    });
+}
+FB_API int fb_comm_destroy(void) { return guarded(fb::g_last_error, [&] { fb::Comm::get().destroy(); }); }
+FB_API int fb_comm_rank(void) { return fb::Comm::get().rank(); }
+FB_API int fb_comm_world(void) { return fb::Comm::get().world(); }
+FB_API int fb_shard_plan(int nbins, unsigned maxdiag, int world, int32_t *row_begin, int32_t *col_begin) {
+    if (!row_begin || !col_begin) { fb::g_last_error = "null argument"; return FB_ERR_ARG; }
+    return guarded(fb::g_last_error, [&] {
+        unsigned md = maxdiag < (unsigned)nbins ? maxdiag : (unsigned)nbins;        // FusedLassoGaussianEstimator.hpp:33
+        if (md > (unsigned)(nbins + 1) / 2 || md <= 1) md = nbins;                  // GFLLibrary.hpp:21-27
+        fb::shard_plan(nbins, (int)md, world, row_begin, col_begin);
     });
 }
 

@@ -1,0 +1,44 @@
+// fb_comm.cuh -- one process per GPU: the process-wide NCCL communicator of the library.
+//
+// The only multi-GPU step on this path is the trail-block ADMM of ONE fused-lasso solve (SURVEY.md section 8e,
+// "trail blocks within one matrix"): the chains of graph_fused_lasso_weight_warm (gfl_graph_fl.c:53-213) are split
+// into equal-cell row blocks and column blocks, one pair per rank, and the consensus terms z - u of the cells where a
+// row block of one rank crosses a column block of another are exchanged once per iteration (grouped ncclSend/ncclRecv
+// over NVLink), plus one small all-reduce of the per-chain residual sums. NCCL is loaded at run time with dlopen
+// (libnccl.so.2, the copy already mapped by torch when the host is Python), so the library itself links cudart only
+// and still loads on a machine without NCCL.
+#pragma once
+#include "fb_util.cuh"
+#include <vector>
+
+namespace fb {
+
+struct CommError : std::runtime_error { using std::runtime_error::runtime_error; };
+
+// Equal-cell split of the band grid (n bins, band width md; md == n is the full triangle) into `world` row blocks and
+// `world` column blocks: row_begin / col_begin get world + 1 entries, block g = [begin[g], begin[g+1]).
+void shard_plan(int n, int md, int world, int *row_begin, int *col_begin);
+
+class Comm {
+public:
+    static Comm &get();
+    bool active() const { return comm_ != nullptr && world_ > 1; }
+    int rank() const { return rank_; }
+    int world() const { return world_; }
+    void unique_id(void *out128);                          // ncclGetUniqueId (rank 0; the host distributes the bytes)
+    void init(int rank, int world, const void *id128);     // ncclCommInitRank on the current device
+    void destroy();
+    void group_start();
+    void group_end();
+    void send(const double *p, size_t n, int peer, cudaStream_t s);
+    void recv(double *p, size_t n, int peer, cudaStream_t s);
+    void allreduce_sum(const double *src, double *dst, size_t n, cudaStream_t s);
+    void bcast(double *p, size_t n, int root, cudaStream_t s);
+private:
+    void load();
+    void *lib_ = nullptr, *comm_ = nullptr;
+    int rank_ = 0, world_ = 1;
+    void *fn_[12] = {};
+};
+
+} // namespace fb

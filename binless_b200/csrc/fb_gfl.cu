@@ -15,6 +15,7 @@
 // The host polls the control block every few iterations; once `done` is set the remaining queued
 // launches return immediately.
 #include "fb_gfl.cuh"
+#include "fb_comm.cuh"
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
@@ -37,11 +38,14 @@ constexpr unsigned FULL = 0xffffffffu;
 __global__ void __launch_bounds__(TILE * 8)
 k_beta(Grid g, const GflCtl *__restrict__ ctl, const double *__restrict__ y, const double *__restrict__ w,
        const double *__restrict__ zr, double *__restrict__ ur, const double *__restrict__ zc,
-       double *__restrict__ uc, double *__restrict__ beta, double *__restrict__ betaT) {
+       double *__restrict__ uc, double *__restrict__ beta, double *__restrict__ betaT,
+       const int r0, const int r1, const int c0, const int c1) {
     if (ctl->done) return;
     const int i0 = blockIdx.y * TILE, j0 = blockIdx.x * TILE;
     // tile must intersect the band 0 <= j-i < md
     if (j0 + TILE - 1 < i0 || j0 - (i0 + TILE - 1) >= g.md) return;
+    // ... and hold a cell of a chain this rank owns (rows [r0, r1) or columns [c0, c1); everything when not sharded)
+    if (!(i0 < r1 && i0 + TILE > r0) && !(j0 < c1 && j0 + TILE > c0)) return;
     __shared__ double s_tcol[TILE][TILE + 1]; // z_col - u_col, indexed [j][i]
     __shared__ double s_beta[TILE][TILE + 1]; // indexed [i][j]
     const int tx = threadIdx.x, ty = threadIdx.y;
@@ -177,7 +181,15 @@ struct Seg {
 // upper (isup) or lower tube edge. Otherwise the carried bounds are updated. One instantiation only, loops that
 // are not on the critical path are not unrolled: the team kernel is instruction-cache bound otherwise.
 constexpr int B = PBR;
-__device__ __forceinline__ bool taut_round(const Frame &f, const double *__restrict__ R, const double lam, Seg &g,
+// 1/m: from the shared-memory table when m < rl, else the same correctly rounded quotient computed in place
+// (LONG chains: the table covers the first rl distances only so that the prefix sums of a 27 000-cell chain fit)
+template <bool LONG>
+__device__ __forceinline__ double recip(const double *__restrict__ R, const int rl, const int m) {
+    if (LONG) return m < rl ? R[m] : 1.0 / (double)m;
+    return R[m];
+}
+template <bool LONG>
+__device__ __forceinline__ bool taut_round(const Frame &f, const double *__restrict__ R, const int rl, const double lam, Seg &g,
                                            const int kEnd, const double aEnd, const int lane,
                                            int &isup, double &slope, int &kend) {
     const double INF = __longlong_as_double(0x7ff0000000000000LL);
@@ -188,7 +200,7 @@ __device__ __forceinline__ bool taut_round(const Frame &f, const double *__restr
     double hmin = INF, lmax = -INF;
     unsigned m = 0;
     if (g.p + 32 * B < kEnd) { // every candidate is an interior point of the chain
-        const double *__restrict__ Rp = R + (kb - g.k0);
+        const int m0 = kb - g.k0;
         double sv[B];
         if (f.dir) {
             const double *__restrict__ Sq = f.S + (f.L - kb);
@@ -202,7 +214,7 @@ __device__ __forceinline__ bool taut_round(const Frame &f, const double *__restr
 #pragma unroll
         for (int b = 0; b < B; ++b) {
             const double base = __fma_rn(sgn, sv[b], off);
-            const double ri = Rp[b];
+            const double ri = recip<LONG>(R, rl, m0 + b);
             const double h = (base + lam) * ri, l = (base - lam) * ri;
             hi[b] = h; lo[b] = l;
             if ((l > hmin) || (h < lmax)) m |= 1u << b;
@@ -214,7 +226,7 @@ __device__ __forceinline__ bool taut_round(const Frame &f, const double *__restr
             const int k = kb + b;
             const int kc = k < kEnd ? k : kEnd;
             const double base = __fma_rn(sgn, f.S[f.dir ? f.L - kc : kc], off);
-            const double ri = R[kc - g.k0];
+            const double ri = recip<LONG>(R, rl, kc - g.k0);
             const bool fixed = (k == kEnd);      // a point of the string, not a tube
             double h = (base + (fixed ? aEnd : lam)) * ri;
             double l = (base - (fixed ? -aEnd : lam)) * ri;
@@ -286,8 +298,9 @@ __device__ __forceinline__ void seg_reset(Seg &g) {
 
 // Lock-step taut string of one chain by the two warps of a team. S holds the prefix sums S[0..L] on entry; on
 // return cell i of the solution is at S[i] for i < split (written by the left warp) and at S[i+1] for i >= split.
+template <bool LONG>
 __device__ __forceinline__ int taut_string_team(double *__restrict__ S, volatile int *__restrict__ ti, const int L,
-                                                const double lam, const double c, const double *__restrict__ R,
+                                                const double lam, const double c, const double *__restrict__ R, const int rl,
                                                 const int side, const int lane, const int bar, int &nrounds) {
     Frame f; f.S = S; f.L = L; f.dir = side; f.SL = S[L];
     Seg sg; sg.k0 = 0; sg.s0 = 0.0; seg_reset(sg);
@@ -299,7 +312,7 @@ __device__ __forceinline__ int taut_string_team(double *__restrict__ S, volatile
         if (kEnd <= sg.p) seg_reset(sg);                               // the other warp's knot moved inside the scanned range
         int isup = 0, kend = 0;
         double slope = 0.0;
-        const bool viol = taut_round(f, R, lam, sg, kEnd, aEnd, lane, isup, slope, kend);
+        const bool viol = taut_round<LONG>(f, R, rl, lam, sg, kEnd, aEnd, lane, isup, slope, kend);
         sg.p += 32 * PBR;
         ++nrounds;
         int status = 0, asign = 0;
@@ -310,7 +323,7 @@ __device__ __forceinline__ int taut_string_team(double *__restrict__ S, volatile
             s0n = f.at(kend) + (isup ? lam : -lam);
         } else if (sg.p >= kEnd) { // the fixed end point was examined without violation: the segment runs up to it
             status = 1; kend = kEnd;
-            val = c + ((f.at(kEnd) - sg.s0) + aEnd) * R[kEnd - sg.k0];
+            val = c + ((f.at(kEnd) - sg.s0) + aEnd) * recip<LONG>(R, rl, kEnd - sg.k0);
         }
         if (lane == 0) { ti[side * 4] = status; ti[side * 4 + 1] = side ? L - kend : kend; ti[side * 4 + 2] = asign; }
         team_sync(bar);
@@ -337,10 +350,12 @@ __device__ __forceinline__ int taut_string_team(double *__restrict__ S, volatile
     return dL;
 }
 
+template <bool LONG>
 __global__ void __launch_bounds__(64 * PROX_MAX_TEAMS, 1)
 k_prox(Grid g, GflCtl *__restrict__ ctl, const double *__restrict__ beta, const double *__restrict__ betaT,
        double *__restrict__ zr, double *__restrict__ ur, double *__restrict__ zc, double *__restrict__ uc,
-       double *__restrict__ partials, int stride, int rlen, long long *__restrict__ trace) {
+       double *__restrict__ partials, int stride, int rlen, long long *__restrict__ trace,
+       const int *__restrict__ list, const int nlist) {
     if (ctl->done) return;
     extern __shared__ double smem[];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -352,11 +367,12 @@ k_prox(Grid g, GflCtl *__restrict__ ctl, const double *__restrict__ beta, const 
     __syncthreads();
     const double alpha = ctl->alpha;
     const double lam = ctl->lam / (alpha / 2.0);
-    const int nchains = g.nchains();
+    const int nchains = list ? nlist : g.nchains();   // sharded: the chains of this rank, longest first
     if (side == 0 && lane == 0) ti[8] = atomicAdd(&ctl->next_chain, 1);
     team_sync(bar);
-    int q = ti[8];
-    while (q < nchains) {
+    int qi = ti[8];
+    while (qi < nchains) {
+        const int q = list ? list[qi] : qi;
         int qnext = 0;
         if (side == 0 && lane == 0) qnext = atomicAdd(&ctl->next_chain, 1); // published after this chain: latency hidden
         long long t0 = 0, t1 = 0, t2 = 0;
@@ -415,7 +431,7 @@ k_prox(Grid g, GflCtl *__restrict__ ctl, const double *__restrict__ beta, const 
             }
             team_sync(bar);
             if (trace) t1 = clock64();
-            split = taut_string_team(S, ti, L, lam, c, R, side, lane, bar, nrounds);
+            split = taut_string_team<LONG>(S, ti, L, lam, c, R, rlen, side, lane, bar, nrounds);
             if (trace) t2 = clock64();
         } else {
             team_sync(bar);
@@ -453,7 +469,44 @@ k_prox(Grid g, GflCtl *__restrict__ ctl, const double *__restrict__ beta, const 
         }
         if (side == 0 && lane == 0) ti[8] = qnext;
         team_sync(bar); // both warps are done with S; the next chain is published
-        q = ti[8];
+        qi = ti[8];
+    }
+}
+
+// --------------------------------------------------------------------------
+// trail-block exchange: pack z - u of the cells another rank's chains cross (with the pending dual rescale applied,
+// exactly the expression k_beta evaluates on the owner), or unpack the received terms into z (u = 0 there).
+// grid (lines, peers); one block walks whole lines.
+// --------------------------------------------------------------------------
+template <int DIR, bool PACK>
+__global__ void __launch_bounds__(256)
+k_exchange(Grid g, const GflCtl *__restrict__ ctl, const ShardRegion *__restrict__ regs, const int64_t *__restrict__ lineoff,
+           double *__restrict__ z, double *__restrict__ u, double *__restrict__ buf, const int zero_u) {
+    if (ctl->idle) return;
+    const ShardRegion r = regs[2 * blockIdx.y + DIR];
+    const int mode = ctl->rescale;
+    const double inflate = ctl->inflate;
+    for (int line = r.l0 + blockIdx.x; line < r.l1; line += gridDim.x) {
+        int lo, hi; int64_t base;
+        if (DIR == 0) {
+            lo = max(r.x0, line); hi = min(r.x1, line + g.row_len(line));
+            base = g.rm_row_start(line) + (lo - line);
+        } else {
+            const int f = g.col_first_row(line);
+            lo = max(r.x0, f); hi = min(r.x1, line + 1);
+            base = g.cm_col_start(line) + (lo - f);
+        }
+        const int64_t off = r.buf_off + lineoff[r.off_idx + (line - r.l0)];
+        for (int x = threadIdx.x; x < hi - lo; x += blockDim.x) {
+            if (PACK) {
+                double uu = u[base + x];
+                if (mode == 1) uu = uu / inflate; else if (mode == 2) uu = uu * inflate;
+                buf[off + x] = z[base + x] - uu;
+            } else {
+                z[base + x] = buf[off + x];
+                if (zero_u) u[base + x] = 0.0;
+            }
+        }
     }
 }
 
@@ -462,7 +515,7 @@ k_prox(Grid g, GflCtl *__restrict__ ctl, const double *__restrict__ beta, const 
 // --------------------------------------------------------------------------
 __global__ void __launch_bounds__(CTL_THREADS)
 k_ctl(GflCtl *ctl, const double *__restrict__ partials, int npart, int64_t ncells, int64_t nz) {
-    if (ctl->done) return;
+    if (ctl->done) { if (threadIdx.x == 0) ctl->idle = 1; return; }
     __shared__ double s_p[CTL_THREADS], s_d[CTL_THREADS];
     double p = 0.0, d = 0.0;
     for (int k = threadIdx.x; k < npart; k += CTL_THREADS) { p += partials[2 * k]; d += partials[2 * k + 1]; }
@@ -551,7 +604,8 @@ GflSolver::GflSolver(int nbins, unsigned maxdiag, cudaStream_t stream) : nbins_(
     beta_.alloc(N); betaT_.alloc(N); zr_.alloc(N); ur_.alloc(N); zc_.alloc(N); uc_.alloc(N);
     if (trapeze_) { yband_.alloc(N); wband_.alloc(N); fillavg_.alloc(1); }
     n_partials_ = 2 * g_.nchains(); // one (primal, dual) pair per warp of a team
-    partials_.alloc(2 * (size_t)std::max(n_partials_, nbins));
+    partials_.alloc(2 * (size_t)n_partials_);
+    if (trapeze_) band_partials_.alloc(2 * (size_t)nbins);
     // k_prox: one warp per chain, the chain's prefix sums in shared memory (8 (Lmax + 1) bytes per warp)
     {
         int dev = 0, smem_max = 0;
@@ -561,18 +615,136 @@ GflSolver::GflSolver(int nbins, unsigned maxdiag, cudaStream_t stream) : nbins_(
         const int lmax = g_.row_len(0);
         prox_stride_ = lmax + 2 + 8;   // S[0..L], one spare slot, 16-int team mailbox
         prox_rlen_ = lmax + 1;
-        prox_warps_ = std::min<int64_t>(PROX_MAX_TEAMS, ((int64_t)smem_max / 8 - prox_rlen_) / (int64_t)prox_stride_);
-        if (prox_warps_ < 1) throw ArgError("chains longer than 14500 cells are not supported by this build of the fused-lasso prox");
+        const int64_t words = (int64_t)smem_max / 8;
+        // the full reciprocal table while two chains still fit beside it; else a 2048-entry table and in-place
+        // quotients beyond it (LONG mode: chains up to ~27 000 cells, one team per SM)
+        constexpr int RT_SHORT = 2048;
+        prox_long_ = (words - prox_rlen_) / prox_stride_ < 2 && prox_rlen_ > RT_SHORT;
+        if (const char *e = std::getenv("FB_PROX_RTAB")) { // test aid: force LONG mode with a table of this size
+            const int v = std::atoi(e);
+            if (v >= 2 && v < prox_rlen_) { prox_long_ = true; prox_rlen_ = v; }
+        } else if (prox_long_) prox_rlen_ = RT_SHORT;
+        prox_warps_ = std::min<int64_t>(PROX_MAX_TEAMS, (words - prox_rlen_) / (int64_t)prox_stride_);
+        if (prox_warps_ < 1) throw ArgError("chains longer than 26990 cells are not supported by this build of the fused-lasso prox");
         prox_warps_ = std::min(prox_warps_, std::max(1, (g_.nchains() + n_sm_ - 1) / n_sm_));
         prox_smem_ = ((size_t)prox_warps_ * prox_stride_ + prox_rlen_) * 8;
-        FB_CUDA(cudaFuncSetAttribute(k_prox, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)prox_smem_));
+        if (prox_long_) FB_CUDA(cudaFuncSetAttribute(k_prox<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)prox_smem_));
+        else FB_CUDA(cudaFuncSetAttribute(k_prox<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)prox_smem_));
         prox_grid_ = std::min(n_sm_, (g_.nchains() + prox_warps_ - 1) / prox_warps_);
     }
     ctl_.alloc(1);
     if (std::getenv("FB_PROX_TRACE")) { trace_.alloc(4 * (size_t)g_.nchains()); trace_.zero(); }
     h_ctl_ = static_cast<GflCtl *>(BlockCache::host().get(sizeof(GflCtl)));
     FB_CUDA(cudaEventCreate(&ev0_)); FB_CUDA(cudaEventCreate(&ev1_));
+    r0_ = c0_ = 0; r1_ = c1_ = g_.n;
+    if (Comm::get().active()) setup_shard();
     reset();
+}
+
+// Row blocks / column blocks of equal cell count, the chains of this rank (longest first) and, per peer, the two
+// regions whose consensus terms cross between the ranks: my rows x its columns (row duals, sent; its rows x my
+// columns, received) and my columns x its rows (column duals).
+void GflSolver::setup_shard() {
+    Comm &cm = Comm::get();
+    sharded_ = true; rank_ = cm.rank(); world_ = cm.world();
+    row_begin_.resize(world_ + 1); col_begin_.resize(world_ + 1);
+    shard_plan(g_.n, g_.md, world_, row_begin_.data(), col_begin_.data());
+    r0_ = row_begin_[rank_]; r1_ = row_begin_[rank_ + 1];
+    c0_ = col_begin_[rank_]; c1_ = col_begin_[rank_ + 1];
+    // chains: row r (r <= n-2) is q = 2r, column j (j >= 1) is q = 2(n-1-j)+1 (Grid::chain)
+    std::vector<std::pair<int, int>> mine; // (-length, q)
+    for (int r = r0_; r < r1_ && r <= g_.n - 2; ++r) mine.push_back({-g_.row_len(r), 2 * r});
+    for (int j = std::max(c0_, 1); j < c1_; ++j) mine.push_back({-g_.col_len(j), 2 * (g_.n - 1 - j) + 1});
+    std::sort(mine.begin(), mine.end());
+    std::vector<int> list(mine.size());
+    for (size_t k = 0; k < mine.size(); ++k) list[k] = mine[k].second;
+    n_list_ = (int)list.size();
+    chain_list_.alloc(std::max<size_t>(1, list.size()));
+    if (n_list_) FB_CUDA(cudaMemcpy(chain_list_.p, list.data(), list.size() * sizeof(int), cudaMemcpyHostToDevice));
+    prox_grid_ = std::max(1, std::min(n_sm_, (n_list_ + prox_warps_ - 1) / prox_warps_));
+    // regions
+    auto line_cells = [&](int dir, int line, int x0, int x1) -> int {
+        int lo, hi;
+        if (dir == 0) { lo = std::max(x0, line); hi = std::min(x1, line + g_.row_len(line)); }
+        else { lo = std::max(x0, g_.col_first_row(line)); hi = std::min(x1, line + 1); }
+        return std::max(0, hi - lo);
+    };
+    auto build = [&](bool sending, std::vector<ShardRegion> &regs, std::vector<int64_t> &lineoff,
+                     std::vector<int64_t> &cnt, std::vector<int64_t> &off) -> int64_t {
+        cnt.assign(world_, 0); off.assign(world_, 0);
+        int64_t total = 0;
+        for (int p = 0; p < world_; ++p) {
+            if (p == rank_) continue;
+            off[p] = total;
+            for (int dir = 0; dir < 2; ++dir) {
+                ShardRegion r;
+                // lines belong to the SENDER: its rows (dir 0) or columns (dir 1); x runs over the RECEIVER's columns / rows
+                const int ls = sending ? rank_ : p, xs = sending ? p : rank_;
+                r.l0 = dir == 0 ? row_begin_[ls] : col_begin_[ls]; r.l1 = dir == 0 ? row_begin_[ls + 1] : col_begin_[ls + 1];
+                r.x0 = dir == 0 ? col_begin_[xs] : row_begin_[xs]; r.x1 = dir == 0 ? col_begin_[xs + 1] : row_begin_[xs + 1];
+                r.buf_off = total; r.off_idx = (int64_t)lineoff.size();
+                int64_t acc = 0;
+                for (int line = r.l0; line < r.l1; ++line) { lineoff.push_back(acc); acc += line_cells(dir, line, r.x0, r.x1); }
+                total += acc;
+                max_lines_ = std::max(max_lines_, r.l1 - r.l0);
+                regs.push_back(r);
+            }
+            cnt[p] = total - off[p];
+        }
+        return total;
+    };
+    std::vector<ShardRegion> sregs, rregs;
+    std::vector<int64_t> soff, roff;
+    const int64_t stot = build(true, sregs, soff, send_cnt_, send_off_);
+    const int64_t rtot = build(false, rregs, roff, recv_cnt_, recv_off_);
+    send_regs_.alloc(sregs.size()); recv_regs_.alloc(rregs.size());
+    FB_CUDA(cudaMemcpy(send_regs_.p, sregs.data(), sregs.size() * sizeof(ShardRegion), cudaMemcpyHostToDevice));
+    FB_CUDA(cudaMemcpy(recv_regs_.p, rregs.data(), rregs.size() * sizeof(ShardRegion), cudaMemcpyHostToDevice));
+    send_lineoff_.alloc(std::max<size_t>(1, soff.size())); recv_lineoff_.alloc(std::max<size_t>(1, roff.size()));
+    if (!soff.empty()) FB_CUDA(cudaMemcpy(send_lineoff_.p, soff.data(), soff.size() * sizeof(int64_t), cudaMemcpyHostToDevice));
+    if (!roff.empty()) FB_CUDA(cudaMemcpy(recv_lineoff_.p, roff.data(), roff.size() * sizeof(int64_t), cudaMemcpyHostToDevice));
+    send_buf_.alloc(std::max<int64_t>(1, stot)); recv_buf_.alloc(std::max<int64_t>(1, rtot));
+    send_buf_.zero(st_); recv_buf_.zero(st_);
+    partials_.zero(st_);   // chains of other ranks contribute exact zeros to the all-reduce
+    partials_all_.alloc(partials_.n);
+}
+
+// z - u of the crossing cells, both directions, to and from every peer
+void GflSolver::exchange(bool zero_u) {
+    Comm &cm = Comm::get();
+    dim3 grid((unsigned)std::min(max_lines_, 4096), (unsigned)(world_ - 1));
+    k_exchange<0, true><<<grid, 256, 0, st_>>>(g_, ctl_.p, send_regs_.p, send_lineoff_.p, zr_.p, ur_.p, send_buf_.p, 0);
+    k_exchange<1, true><<<grid, 256, 0, st_>>>(g_, ctl_.p, send_regs_.p, send_lineoff_.p, zc_.p, uc_.p, send_buf_.p, 0);
+    cm.group_start();
+    for (int p = 0; p < world_; ++p) {
+        if (p == rank_) continue;
+        if (send_cnt_[p]) cm.send(send_buf_.p + send_off_[p], (size_t)send_cnt_[p], p, st_);
+        if (recv_cnt_[p]) cm.recv(recv_buf_.p + recv_off_[p], (size_t)recv_cnt_[p], p, st_);
+    }
+    cm.group_end();
+    k_exchange<0, false><<<grid, 256, 0, st_>>>(g_, ctl_.p, recv_regs_.p, recv_lineoff_.p, zr_.p, ur_.p, recv_buf_.p, zero_u ? 1 : 0);
+    k_exchange<1, false><<<grid, 256, 0, st_>>>(g_, ctl_.p, recv_regs_.p, recv_lineoff_.p, zc_.p, uc_.p, recv_buf_.p, zero_u ? 1 : 0);
+    kernel_launches += 4;
+}
+
+// every rank ends with the whole array: the row blocks (row-major array) or column blocks (column-major array)
+void GflSolver::allgather_rows(double *a) {
+    Comm &cm = Comm::get();
+    cm.group_start();
+    for (int p = 0; p < world_; ++p) {
+        const int64_t b = g_.rm_row_start(row_begin_[p]), e = g_.rm_row_start(row_begin_[p + 1]);
+        if (e > b) cm.bcast(a + b, (size_t)(e - b), p, st_);
+    }
+    cm.group_end();
+}
+void GflSolver::allgather_cols(double *a) {
+    Comm &cm = Comm::get();
+    cm.group_start();
+    for (int p = 0; p < world_; ++p) {
+        const int64_t b = g_.cm_col_start(col_begin_[p]), e = g_.cm_col_start(col_begin_[p + 1]);
+        if (e > b) cm.bcast(a + b, (size_t)(e - b), p, st_);
+    }
+    cm.group_end();
 }
 
 GflSolver::~GflSolver() {
@@ -591,11 +763,20 @@ void GflSolver::reset() {
 void GflSolver::iteration(const double *y, const double *w, int parity) {
     (void)parity;
     dim3 tb(TILE, 8), tg((g_.n + TILE - 1) / TILE, (g_.n + TILE - 1) / TILE);
-    k_beta<<<tg, tb, 0, st_>>>(g_, ctl_.p, y, w, zr_.p, ur_.p, zc_.p, uc_.p, beta_.p, betaT_.p);
-    k_prox<<<prox_grid_, 64 * prox_warps_, prox_smem_, st_>>>(g_, ctl_.p, beta_.p, betaT_.p, zr_.p, ur_.p, zc_.p, uc_.p,
-                                                             partials_.p, prox_stride_, prox_rlen_, trace_.p);
-    k_ctl<<<1, CTL_THREADS, 0, st_>>>(ctl_.p, partials_.p, n_partials_, g_.ncells, 2 * g_.ncells - 2);
+    k_beta<<<tg, tb, 0, st_>>>(g_, ctl_.p, y, w, zr_.p, ur_.p, zc_.p, uc_.p, beta_.p, betaT_.p, r0_, r1_, c0_, c1_);
+    const int *list = sharded_ ? chain_list_.p : nullptr;
+    if (prox_long_)
+        k_prox<true><<<prox_grid_, 64 * prox_warps_, prox_smem_, st_>>>(g_, ctl_.p, beta_.p, betaT_.p, zr_.p, ur_.p, zc_.p, uc_.p,
+                                                                       partials_.p, prox_stride_, prox_rlen_, trace_.p, list, n_list_);
+    else
+        k_prox<false><<<prox_grid_, 64 * prox_warps_, prox_smem_, st_>>>(g_, ctl_.p, beta_.p, betaT_.p, zr_.p, ur_.p, zc_.p, uc_.p,
+                                                                        partials_.p, prox_stride_, prox_rlen_, trace_.p, list, n_list_);
+    // sharded: the residual sums of every chain on every rank (exactly one rank contributes a non-zero term per
+    // slot, so the sum is exact and k_ctl reduces the same numbers in the same order everywhere)
+    if (sharded_) Comm::get().allreduce_sum(partials_.p, partials_all_.p, 2 * (size_t)n_partials_, st_);
+    k_ctl<<<1, CTL_THREADS, 0, st_>>>(ctl_.p, sharded_ ? partials_all_.p : partials_.p, n_partials_, g_.ncells, 2 * g_.ncells - 2);
     kernel_launches += 3;
+    if (sharded_) exchange(false);
 }
 
 int GflSolver::optimize(const double *d_y_tri, const double *d_w_tri, double lam2, double converge) {
@@ -613,9 +794,10 @@ int GflSolver::optimize(const double *d_y_tri, const double *d_w_tri, double lam
     c.alpha = alpha; c.lam = lam2; c.converge = converge; c.inflate = inflate;
     c.presnorm = c.dresnorm = 0; c.step = 1; c.maxsteps = ninner_max;
     c.done = !(c.step < c.maxsteps && (converge + 1) > converge);
-    c.rescale = 0; c.next_chain = 0;
+    c.rescale = 0; c.next_chain = 0; c.idle = 0;
     *h_ctl_ = c;
     FB_CUDA(cudaMemcpyAsync(ctl_.p, h_ctl_, sizeof(GflCtl), cudaMemcpyHostToDevice, st_));
+    if (sharded_) exchange(true);   // whatever state the ranks start from: remote slots hold z - u of their owner, u = 0
     int parity = 0;
     bool done = c.done != 0;
     while (!done) {
@@ -636,9 +818,10 @@ int GflSolver::optimize(const double *d_y_tri, const double *d_w_tri, double lam
         last_steps = h_ctl_->step;
     } else last_steps = 1;
     counter += last_steps;
+    if (sharded_) allgather_rows(beta_.p);   // every rank continues with the whole solution
     if (trapeze_) { // average of the far region (fill_triangle)
-        k_band_outside_sums<<<nbins_, 256, 0, st_>>>(g_, nbins_, d_y_tri, d_w_tri, partials_.p);
-        k_band_avg<<<1, 32, 0, st_>>>(nbins_, partials_.p, fillavg_.p);
+        k_band_outside_sums<<<nbins_, 256, 0, st_>>>(g_, nbins_, d_y_tri, d_w_tri, band_partials_.p);
+        k_band_avg<<<1, 32, 0, st_>>>(nbins_, band_partials_.p, fillavg_.p);
         kernel_launches += 2;
     }
     FB_CUDA(cudaEventRecord(ev1_, st_));
@@ -663,6 +846,9 @@ void GflSolver::get_beta_full(double *d_out_tri) {
 // (cm index >= 1 maps to slot N-1 + cm-1)
 void GflSolver::export_state(double *h_beta, double *h_z, double *h_u) {
     const int64_t N = g_.ncells;
+    if (sharded_ && (h_z || h_u)) { // collect the duals of every rank's chains
+        allgather_rows(zr_.p); allgather_rows(ur_.p); allgather_cols(zc_.p); allgather_cols(uc_.p);
+    }
     FB_CUDA(cudaStreamSynchronize(st_));
     if (h_beta) FB_CUDA(cudaMemcpy(h_beta, beta_.p, N * sizeof(double), cudaMemcpyDeviceToHost));
     if (h_z) {

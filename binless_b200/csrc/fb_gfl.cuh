@@ -8,6 +8,7 @@
 // (paths relative to /root/reference/binless/src). See DESIGN.md for the layout.
 #pragma once
 #include "fb_util.cuh"
+#include <vector>
 
 namespace fb {
 
@@ -54,6 +55,16 @@ struct GflCtl {
     int step, maxsteps, done;
     int rescale;      // pending dual rescale: 0 none, 1 u /= inflate, 2 u *= inflate
     int next_chain;   // work queue head of k_prox (longest chains first)
+    int idle;         // set by k_ctl on launches queued after convergence: the trail-block exchange is skipped
+};
+
+// Trail-block sharding (one process per GPU): the cells {line in [l0,l1), x in [x0,x1)} of the
+// band, packed line by line, that one rank sends to / receives from one peer. dir 0: lines are rows (row-major arrays,
+// x = column); dir 1: lines are columns (column-major arrays, x = row).
+struct ShardRegion {
+    int l0, l1, x0, x1;
+    int64_t buf_off;   // first packed cell in the exchange buffer
+    int64_t off_idx;   // first entry of this region in the line-offset array
 };
 
 // One GFLLibrary strategy object: persistent beta / z / u / alpha (warm start)
@@ -90,7 +101,23 @@ private:
     bool trapeze_;
     cudaStream_t st_;
     DevBuf<double> beta_, betaT_, zr_, ur_, zc_, uc_, yband_, wband_, fillavg_;
-    DevBuf<double> partials_;
+    DevBuf<double> partials_, partials_all_, band_partials_;
+    // trail-block sharding over the ranks of fb::Comm (inactive: one rank owns every chain)
+    bool sharded_ = false;
+    int rank_ = 0, world_ = 1;
+    int r0_ = 0, r1_ = 0, c0_ = 0, c1_ = 0;          // rows / columns whose chains this rank owns
+    std::vector<int> row_begin_, col_begin_;
+    std::vector<int64_t> send_cnt_, send_off_, recv_cnt_, recv_off_;   // per rank, in doubles
+    DevBuf<int> chain_list_;
+    int n_list_ = 0;
+    DevBuf<ShardRegion> send_regs_, recv_regs_;
+    DevBuf<int64_t> send_lineoff_, recv_lineoff_;
+    DevBuf<double> send_buf_, recv_buf_;
+    int max_lines_ = 1;
+    void setup_shard();
+    void exchange(bool zero_u);
+    void allgather_rows(double *rm_array);
+    void allgather_cols(double *cm_array);
     DevBuf<GflCtl> ctl_;
     DevBuf<long long> trace_;         // FB_PROX_TRACE development aid
     GflCtl *h_ctl_ = nullptr;          // pinned
@@ -98,6 +125,7 @@ private:
     int n_partials_ = 0;
     int n_sm_ = 148, prox_warps_ = 1, prox_grid_ = 1, prox_stride_ = 0, prox_rlen_ = 0;
     size_t prox_smem_ = 0;
+    bool prox_long_ = false;           // reciprocal table shorter than the longest chain
     cudaEvent_t ev0_, ev1_;
     void iteration(const double *y, const double *w, int parity);
 };

@@ -54,7 +54,8 @@ enum {
     FB_ERR_CUDA = 2,    /* CUDA runtime failure or no device */
     FB_ERR_STATE = 3,   /* call order violation (e.g. difference before signal/restore) */
     FB_ERR_NUMERIC = 4, /* e.g. "decomposition failed" (QuadProgGAMLibrary.cpp:21) */
-    FB_ERR_INTERRUPT = 5
+    FB_ERR_INTERRUPT = 5,
+    FB_ERR_COMM = 6     /* NCCL missing or a collective failed (multi-GPU only) */
 };
 
 #define FB_DECAY_K 50       /* Config<Decay,GAM>::K, fast_decay.hpp:25 */
@@ -195,6 +196,27 @@ FB_API int FB_NAME(gfl_solve)(int nbins, unsigned maxdiag, const double *y, cons
 /* Device and pinned-host blocks of destroyed handles are kept in a size-keyed cache (cudaMalloc / cudaFree cost
  * milliseconds per call and fast_binless is called once per locus); this returns them to the driver. */
 FB_API void FB_NAME(release_cached_memory)(void);
+
+/* Multi-GPU, one process per GPU ("trail blocks within one matrix"; BASELINE.json configs 4-5).
+ * The reference has no counterpart: its solve, graph_fused_lasso_weight_warm (gfl_graph_fl.c:53-213), is one thread.
+ * After fb_comm_init every fused-lasso solve of this process (inside fb_run_signal / fb_run_difference / fb_eval_cv /
+ * fb_sweep_lambda / fb_gfl_solve) is shared by the `world` processes: the row chains and the column chains of the
+ * trail decomposition (GFLLibraryTriangleImpl.cpp:7-35) are split into `world` row blocks and column blocks of equal
+ * cell count (fb_shard_plan), rank r runs update_z / update_u (gfl_graph_fl.c:267-327) for the chains of block r, the
+ * terms z - u of the cells where its blocks cross those of another rank are exchanged once per iteration
+ * (ncclSend / ncclRecv) and the per-chain residual sums are all-reduced, so every rank takes the same convergence
+ * and penalty decisions as the single-GPU run and the iterates are identical bit for bit. Every rank must make the
+ * same calls with the same inputs and gets the complete outputs. The IRLS legs are replicated, not sharded.
+ *   fb_comm_unique_id : rank 0 obtains the 128-byte NCCL id; the host (torch.distributed, MPI, a file) hands it round
+ *   fb_comm_init      : joins the communicator on the CURRENT CUDA device; world == 1 switches sharding off
+ *   fb_shard_plan     : host only (no device needed): block g owns rows [row_begin[g], row_begin[g+1]) and columns
+ *                       [col_begin[g], col_begin[g+1]); arrays of world + 1 entries */
+FB_API int FB_NAME(comm_unique_id)(void *id128);
+FB_API int FB_NAME(comm_init)(int rank, int world, const void *id128);
+FB_API int FB_NAME(comm_destroy)(void);
+FB_API int FB_NAME(comm_rank)(void);
+FB_API int FB_NAME(comm_world)(void);
+FB_API int FB_NAME(shard_plan)(int nbins, unsigned maxdiag, int world, int32_t *row_begin, int32_t *col_begin);
 
 FB_API int FB_NAME(set_interrupt_cb)(fb_handle *h, int (*cb)(void *), void *arg);
 

@@ -1247,6 +1247,39 @@ FB_API int fbo_sweep_lambda(fb_handle *h, const fb_params *p, int nlam, const do
 }
 FB_API int64_t fbo_kernel_launches(const fb_handle *) { return 0; }
 FB_API void fbo_release_cached_memory(void) {}
+
+/* The multi-GPU entry points of the ABI. The reference is one thread in one process (gfl_graph_fl.c:53-213), so the
+ * oracle is always a single rank; fbo_shard_plan restates the equal-cell split by counting cells line by line (the
+ * product uses the closed-form offsets) so that the host-side tests can compare the two. */
+FB_API int fbo_comm_unique_id(void *) { g_create_error = "the CPU oracle is a single rank"; return 6; }
+FB_API int fbo_comm_init(int rank, int world, const void *) {
+    if (rank == 0 && world == 1) return FB_OK;
+    g_create_error = "the CPU oracle is a single rank"; return 6;
+}
+FB_API int fbo_comm_destroy(void) { return FB_OK; }
+FB_API int fbo_comm_rank(void) { return 0; }
+FB_API int fbo_comm_world(void) { return 1; }
+FB_API int fbo_shard_plan(int nbins, unsigned maxdiag, int world, int32_t *row_begin, int32_t *col_begin) {
+    if (nbins < 1 || world < 1 || !row_begin || !col_begin) return FB_ERR_ARG;
+    unsigned md = maxdiag < (unsigned)nbins ? maxdiag : (unsigned)nbins;
+    if (md > (unsigned)(nbins + 1) / 2 || md <= 1) md = nbins;
+    long long total = 0;
+    for (int i = 0; i < nbins; ++i) total += std::min<long long>(md, nbins - i);
+    for (int pass = 0; pass < 2; ++pass) {
+        int32_t *out = pass ? col_begin : row_begin;
+        long long before = 0; int line = 0;
+        for (int k = 0; k < world; ++k) {
+            const long long target = (total * k + world - 1) / world;
+            while (line < nbins && before < target) {
+                before += pass ? std::min<long long>(md, line + 1) : std::min<long long>(md, nbins - line);
+                ++line;
+            }
+            out[k] = line;
+        }
+        out[world] = nbins; out[0] = 0;
+    }
+    return FB_OK;
+}
 FB_API int fbo_set_interrupt_cb(fb_handle *h, int (*cb)(void *), void *arg) { h->m.interrupt_cb = cb; h->m.interrupt_arg = arg; return FB_OK; }
 
 FB_API int fbo_gfl_solve(int nbins, unsigned maxdiag, const double *y, const double *w, double lam2,

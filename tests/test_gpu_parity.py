@@ -126,6 +126,23 @@ def test_gfl_solve_matches_oracle(gpu_lib, oracle, n, lam, conv, maxsteps, md):
         assert maxabs(a[k], b[k]) < ATOL, k
 
 
+@pytest.mark.parametrize("n,lam,rtab", [(200, 2.5, 4), (300, 50.0, 16), (120, 1.3, 2)])
+def test_gfl_long_chain_mode_matches_oracle(gpu_lib, oracle, monkeypatch, n, lam, rtab):
+    """The long-chain variant of the prox kernel (reciprocal table shorter than the chain, as used above ~14 000
+    bins) forced at a small size: identical steps and solution."""
+    rng = np.random.default_rng(n)
+    nc = n * (n + 1) // 2
+    y = rng.normal(size=nc); w = rng.uniform(0, 3, size=nc); w[rng.random(nc) < 0.2] = 0
+    a = gfl_solve(oracle, n, y, w, lam, 1e-4, 30000, 0)
+    ref = gfl_solve(gpu_lib, n, y, w, lam, 1e-4, 30000, 0)
+    monkeypatch.setenv("FB_PROX_RTAB", str(rtab))
+    b = gfl_solve(gpu_lib, n, y, w, lam, 1e-4, 30000, 0)
+    assert a["steps"] == b["steps"] and a["alpha"] == b["alpha"]
+    for k in ("beta", "z", "u", "beta_full"):
+        assert maxabs(a[k], b[k]) < ATOL, k
+        assert np.array_equal(ref[k], b[k]), k       # 1/m is the same correctly rounded value either way
+
+
 def test_gfl_warm_start_chain(gpu_lib, oracle):
     n = 120; nc = n * (n + 1) // 2
     rng = np.random.default_rng(3)
