@@ -82,7 +82,12 @@ FB_API int fb_gfl_solve(int nbins, unsigned maxdiag, const double *y, const doub
             throw fb::CudaError("no CUDA device available (there is no CPU fallback)");
         if (!y || !w || !st) throw fb::ArgError("null argument");
         const size_t nc = (size_t)nbins * (nbins + 1) / 2;
-        fb::GflSolver s(nbins, maxdiag, 0);
+        struct Stream { // a real stream (ordered with the default stream): the ADMM loop is captured into a graph
+            cudaStream_t st = nullptr;
+            Stream() { FB_CUDA(cudaStreamCreate(&st)); }
+            ~Stream() { if (st) cudaStreamDestroy(st); }
+        } stream;
+        fb::GflSolver s(nbins, maxdiag, stream.st);
         s.ninner_max = maxsteps;
         fb::DevBuf<double> dy(nc), dw(nc), dout(nc);
         dy.upload(y, nc); dw.upload(w, nc);

@@ -51,6 +51,7 @@ k_beta(Grid g, const GflCtl *__restrict__ ctl, const double *__restrict__ y, con
     const int tx = threadIdx.x, ty = threadIdx.y;
     const double alpha = ctl->alpha, inflate = ctl->inflate;
     const int mode = ctl->rescale;
+    if (!y) { y = ctl->y; w = ctl->w; }   // captured iteration: the inputs of the current solve
 
     // phase A: column duals, coalesced along i in column-major storage
     for (int jj = ty; jj < TILE; jj += 8) {
@@ -513,9 +514,10 @@ k_exchange(Grid g, const GflCtl *__restrict__ ctl, const ShardRegion *__restrict
 // --------------------------------------------------------------------------
 // residual norms, convergence, varying penalty (gfl_graph_fl.c:159-181)
 // --------------------------------------------------------------------------
+template <bool GRAPH>
 __global__ void __launch_bounds__(CTL_THREADS)
-k_ctl(GflCtl *ctl, const double *__restrict__ partials, int npart, int64_t ncells, int64_t nz) {
-    if (ctl->done) { if (threadIdx.x == 0) ctl->idle = 1; return; }
+k_ctl(GflCtl *ctl, const double *__restrict__ partials, int npart, int64_t ncells, int64_t nz, cudaGraphConditionalHandle cond) {
+    if (ctl->done) { if (threadIdx.x == 0) { ctl->idle = 1; if (GRAPH) cudaGraphSetConditional(cond, 0); } return; }
     __shared__ double s_p[CTL_THREADS], s_d[CTL_THREADS];
     double p = 0.0, d = 0.0;
     for (int k = threadIdx.x; k < npart; k += CTL_THREADS) { p += partials[2 * k]; d += partials[2 * k + 1]; }
@@ -538,7 +540,9 @@ k_ctl(GflCtl *ctl, const double *__restrict__ partials, int npart, int64_t ncell
         ++step;
         ctl->step = step;
         ctl->next_chain = 0; // work queue of the next k_prox launch
-        ctl->done = !(step < ctl->maxsteps && cur > ctl->converge);
+        const int done = !(step < ctl->maxsteps && cur > ctl->converge);
+        ctl->done = done;
+        if (GRAPH) cudaGraphSetConditional(cond, done ? 0u : 1u);   // the WHILE node runs the next iteration or stops
     }
 }
 
@@ -638,6 +642,8 @@ GflSolver::GflSolver(int nbins, unsigned maxdiag, cudaStream_t stream) : nbins_(
     FB_CUDA(cudaEventCreate(&ev0_)); FB_CUDA(cudaEventCreate(&ev1_));
     r0_ = c0_ = 0; r1_ = c1_ = g_.n;
     if (Comm::get().active()) setup_shard();
+    // the polling loop stays for the sharded solve (collectives between the kernels) and the trace aid
+    use_graph_ = !sharded_ && !trace_.p && st_ != nullptr && !std::getenv("FB_NO_GRAPH");
     reset();
 }
 
@@ -749,6 +755,8 @@ void GflSolver::allgather_cols(double *a) {
 
 GflSolver::~GflSolver() {
     cudaStreamSynchronize(st_); // buffers go back to the block cache only when nothing uses them any more
+    if (graph_exec_) cudaGraphExecDestroy(graph_exec_);
+    if (graph_) cudaGraphDestroy(graph_);
     if (h_ctl_) BlockCache::host().put(h_ctl_, sizeof(GflCtl));
     cudaEventDestroy(ev0_); cudaEventDestroy(ev1_);
 }
@@ -760,8 +768,7 @@ void GflSolver::reset() {
     betaT_.zero(st_);
 }
 
-void GflSolver::iteration(const double *y, const double *w, int parity) {
-    (void)parity;
+void GflSolver::launch_iteration(const double *y, const double *w, bool in_graph) {
     dim3 tb(TILE, 8), tg((g_.n + TILE - 1) / TILE, (g_.n + TILE - 1) / TILE);
     k_beta<<<tg, tb, 0, st_>>>(g_, ctl_.p, y, w, zr_.p, ur_.p, zc_.p, uc_.p, beta_.p, betaT_.p, r0_, r1_, c0_, c1_);
     const int *list = sharded_ ? chain_list_.p : nullptr;
@@ -774,9 +781,35 @@ void GflSolver::iteration(const double *y, const double *w, int parity) {
     // sharded: the residual sums of every chain on every rank (exactly one rank contributes a non-zero term per
     // slot, so the sum is exact and k_ctl reduces the same numbers in the same order everywhere)
     if (sharded_) Comm::get().allreduce_sum(partials_.p, partials_all_.p, 2 * (size_t)n_partials_, st_);
-    k_ctl<<<1, CTL_THREADS, 0, st_>>>(ctl_.p, sharded_ ? partials_all_.p : partials_.p, n_partials_, g_.ncells, 2 * g_.ncells - 2);
-    kernel_launches += 3;
+    const double *parts = sharded_ ? partials_all_.p : partials_.p;
+    if (in_graph) k_ctl<true><<<1, CTL_THREADS, 0, st_>>>(ctl_.p, parts, n_partials_, g_.ncells, 2 * g_.ncells - 2, cond_);
+    else k_ctl<false><<<1, CTL_THREADS, 0, st_>>>(ctl_.p, parts, n_partials_, g_.ncells, 2 * g_.ncells - 2, cond_);
     if (sharded_) exchange(false);
+}
+
+void GflSolver::iteration(const double *y, const double *w, int parity) {
+    (void)parity;
+    launch_iteration(y, w, false);
+    kernel_launches += 3;
+}
+
+// One iteration captured into the body of a WHILE conditional node (CUDA >= 12.4). The kernels read y / w from the
+// control block, so the same executable graph serves every solve of this object.
+void GflSolver::build_graph() {
+    FB_CUDA(cudaGraphCreate(&graph_, 0));
+    FB_CUDA(cudaGraphConditionalHandleCreate(&cond_, graph_, 1, cudaGraphCondAssignDefault));
+    cudaGraphNodeParams np = {};
+    np.type = cudaGraphNodeTypeConditional;
+    np.conditional.handle = cond_;
+    np.conditional.type = cudaGraphCondTypeWhile;
+    np.conditional.size = 1;
+    cudaGraphNode_t node;
+    FB_CUDA(cudaGraphAddNode(&node, graph_, nullptr, 0, &np));
+    cudaGraph_t body = np.conditional.phGraph_out[0];
+    FB_CUDA(cudaStreamBeginCaptureToGraph(st_, body, nullptr, nullptr, 0, cudaStreamCaptureModeThreadLocal));
+    launch_iteration(nullptr, nullptr, true);
+    FB_CUDA(cudaStreamEndCapture(st_, nullptr));
+    FB_CUDA(cudaGraphInstantiate(&graph_exec_, graph_, 0));
 }
 
 int GflSolver::optimize(const double *d_y_tri, const double *d_w_tri, double lam2, double converge) {
@@ -795,11 +828,21 @@ int GflSolver::optimize(const double *d_y_tri, const double *d_w_tri, double lam
     c.presnorm = c.dresnorm = 0; c.step = 1; c.maxsteps = ninner_max;
     c.done = !(c.step < c.maxsteps && (converge + 1) > converge);
     c.rescale = 0; c.next_chain = 0; c.idle = 0;
+    c.y = y; c.w = w;
     *h_ctl_ = c;
     FB_CUDA(cudaMemcpyAsync(ctl_.p, h_ctl_, sizeof(GflCtl), cudaMemcpyHostToDevice, st_));
     if (sharded_) exchange(true);   // whatever state the ranks start from: remote slots hold z - u of their owner, u = 0
     int parity = 0;
     bool done = c.done != 0;
+    if (!done && use_graph_) {
+        if (!graph_exec_) build_graph();
+        FB_CUDA(cudaGraphLaunch(graph_exec_, st_));
+        FB_CUDA(cudaMemcpyAsync(h_ctl_, ctl_.p, sizeof(GflCtl), cudaMemcpyDeviceToHost, st_));
+        FB_CUDA(cudaStreamSynchronize(st_));
+        if (!h_ctl_->done) throw CudaError("the captured ADMM loop ended without setting done");
+        kernel_launches += 3 * (int64_t)(h_ctl_->step - 1);
+        done = true;
+    }
     while (!done) {
         for (int b = 0; b < POLL_BATCH; ++b) { iteration(y, w, parity); parity ^= 1; }
         FB_LAUNCH_CHECK();

@@ -56,6 +56,7 @@ struct GflCtl {
     int rescale;      // pending dual rescale: 0 none, 1 u /= inflate, 2 u *= inflate
     int next_chain;   // work queue head of k_prox (longest chains first)
     int idle;         // set by k_ctl on launches queued after convergence: the trail-block exchange is skipped
+    const double *y, *w;   // inputs of the running solve (the kernels of the captured iteration read them from here)
 };
 
 // Trail-block sharding (one process per GPU): the cells {line in [l0,l1), x in [x0,x1)} of the
@@ -127,7 +128,15 @@ private:
     size_t prox_smem_ = 0;
     bool prox_long_ = false;           // reciprocal table shorter than the longest chain
     cudaEvent_t ev0_, ev1_;
+    // the whole ADMM loop as ONE graph launch: a WHILE conditional node whose body is one iteration, the condition
+    // set on the device by k_ctl (no host polling, no launches queued past convergence)
+    bool use_graph_ = false;
+    cudaGraph_t graph_ = nullptr;
+    cudaGraphExec_t graph_exec_ = nullptr;
+    cudaGraphConditionalHandle cond_ = 0;
+    void build_graph();
     void iteration(const double *y, const double *w, int parity);
+    void launch_iteration(const double *y, const double *w, bool in_graph);
 };
 
 } // namespace fb

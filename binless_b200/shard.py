@@ -30,3 +30,30 @@ def run_sharded(units: Sequence, fn: Callable, rank: int = 0, world_size: int = 
     dist.all_gather_object(bucket, local)
     flat = [p for part in bucket for p in part]
     return [r for _, r in sorted(flat, key=lambda p: p[0])]
+
+
+# ---- trail-block sharding of ONE fused-lasso solve (include/fastbinless.h: fb_comm_init, fb_shard_plan) -------------
+# Host-side mirror of the geometry the CUDA library uses (binless_b200/csrc/fb_gfl.cu: GflSolver::setup_shard); the
+# tests check the library's plan against it and run the exchange pattern over gloo.
+def band_width(nbins: int, maxdiag: int = 0) -> int:
+    """Width of the solved band: the trapeze variant iff 1 < maxdiag <= (nbins+1)/2 (GFLLibrary.hpp:21-27)."""
+    md = min(int(maxdiag), nbins)
+    return nbins if (md > (nbins + 1) // 2 or md <= 1) else md
+
+
+def crossing_cells(nbins: int, md: int, row_begin, col_begin, sender: int, receiver: int, direction: int):
+    """Cells (i, j) whose consensus term z - u the sender owns and the receiver's chains need, in packing order.
+
+    direction 0: the sender's ROW chains (rows of its row block) crossing the receiver's column block;
+    direction 1: the sender's COLUMN chains crossing the receiver's row block."""
+    import numpy as np
+    out = []
+    if direction == 0:
+        for i in range(row_begin[sender], row_begin[sender + 1]):
+            lo = max(col_begin[receiver], i); hi = min(col_begin[receiver + 1], i + md, nbins)
+            out += [(i, j) for j in range(lo, hi)]
+    else:
+        for j in range(col_begin[sender], col_begin[sender + 1]):
+            lo = max(row_begin[receiver], j - md + 1, 0); hi = min(row_begin[receiver + 1], j + 1)
+            out += [(i, j) for i in range(lo, hi)]
+    return np.array(out, dtype=np.int64).reshape(-1, 2)

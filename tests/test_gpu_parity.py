@@ -310,3 +310,17 @@ def test_csv_out_matches_oracle(gpu_lib, oracle, tmp_path):
     assert np.abs(a - b).max() <= 1.0001e-4            # 4 printed decimals: at most one unit in the last place
     assert np.mean(np.array(lg[1:]) == np.array(lo[1:])) > 0.999
     assert all(len(l.split(",")) == 7 and all(len(x.split(".")[1]) == 4 for x in l.split(",")) for l in lg[1:50])
+
+
+def test_trail_block_sharding_on_two_gpus():
+    """Two processes, one per GPU, share every fused-lasso solve over the library's NCCL communicator; the results
+    must equal the single-GPU ones bit for bit (tools/shard_check.py). Needs two devices."""
+    import subprocess
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (run on a --gpus 2 box); the host-side logic is covered by tests/test_trail_shard.py")
+    port = 29600 + os.getpid() % 300
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                        "--master-addr", "127.0.0.1", "--master-port", str(port),
+                        os.path.join(ROOT, "tools", "shard_check.py")], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "SHARD CHECK PASS" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
