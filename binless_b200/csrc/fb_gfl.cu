@@ -138,7 +138,10 @@ __device__ __forceinline__ double scan_sum_incl(double v, int lane) {
 // bounds are found before the warp scan, those against earlier lanes / earlier rounds after it with B
 // independent compares. TAIL = false requires p + 32*B < kEnd (every candidate is an interior point).
 // --------------------------------------------------------------------------
-constexpr int PBR = 5;          // 160 candidates per round (the average segment is ~45 cells)
+#ifndef FB_PBR
+#define FB_PBR 5
+#endif
+constexpr int PBR = FB_PBR;     // 32 * PBR candidates per round (the average segment is ~45 cells); odd: conflict-free
 constexpr int PB = 7, PW = 32 * PB;   // run length of the blocked prefix-sum pass
 
 __device__ __forceinline__ double dmin_(double a, double b) { return b < a ? b : a; }

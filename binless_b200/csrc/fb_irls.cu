@@ -174,15 +174,26 @@ k_fin_bias(Tri t, int ntI, int ntJ, const double *__restrict__ part, double *__r
     const int tj_min = ((r / TILE_I) * TILE_I) / TILE_J;
     int ti_max = ((r / TILE_J) * TILE_J + TILE_J - 1) / TILE_I;
     if (ti_max > ntI - 1) ti_max = ntI - 1;
+    // fixed summation order (dataset, then row partials by tile column, then column partials by tile row); the loads
+    // of eight terms are issued together so that the chain of additions, not the memory latency, sets the pace
     double a = 0.0, b = 0.0;
+    const double2 *rp = reinterpret_cast<const double2 *>(rowpart), *cp = reinterpret_cast<const double2 *>(colpart);
     for (int d = 0; d < t.D; ++d) {
-        for (int tJ = tj_min; tJ < ntJ; ++tJ) {
-            const int64_t p = ((int64_t)(d * ntJ + tJ) * n + r) * 2;
-            a += rowpart[p]; b += rowpart[p + 1];
+        for (int tJ = tj_min; tJ < ntJ; tJ += 8) {
+            double2 v[8];
+#pragma unroll
+            for (int q = 0; q < 8; ++q)
+                v[q] = (tJ + q < ntJ) ? __ldg(rp + ((int64_t)(d * ntJ + tJ + q) * n + r)) : make_double2(0.0, 0.0);
+#pragma unroll
+            for (int q = 0; q < 8; ++q) if (tJ + q < ntJ) { a += v[q].x; b += v[q].y; }
         }
-        for (int tI = 0; tI <= ti_max; ++tI) {
-            const int64_t p = ((int64_t)(d * ntI + tI) * n + r) * 2;
-            a += colpart[p]; b += colpart[p + 1];
+        for (int tI = 0; tI <= ti_max; tI += 8) {
+            double2 v[8];
+#pragma unroll
+            for (int q = 0; q < 8; ++q)
+                v[q] = (tI + q <= ti_max) ? __ldg(cp + ((int64_t)(d * ntI + tI + q) * n + r)) : make_double2(0.0, 0.0);
+#pragma unroll
+            for (int q = 0; q < 8; ++q) if (tI + q <= ti_max) { a += v[q].x; b += v[q].y; }
         }
     }
     items[2 * r] = a; items[2 * r + 1] = b;
