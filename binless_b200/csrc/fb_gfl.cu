@@ -354,19 +354,22 @@ __device__ __forceinline__ int taut_string_team(double *__restrict__ S, volatile
     return dL;
 }
 
-template <bool LONG>
+// GS: the prefix sums of a chain live in a per-team slot of global scratch (L1/L2 resident) instead of shared memory,
+// which then holds only the reciprocal table: ten teams per SM whatever the chain length.
+template <bool LONG, bool GS>
 __global__ void __launch_bounds__(64 * PROX_MAX_TEAMS, 1)
 k_prox(Grid g, GflCtl *__restrict__ ctl, const double *__restrict__ beta, const double *__restrict__ betaT,
        double *__restrict__ zr, double *__restrict__ ur, double *__restrict__ zc, double *__restrict__ uc,
        double *__restrict__ partials, int stride, int rlen, long long *__restrict__ trace,
-       const int *__restrict__ list, const int nlist) {
+       const int *__restrict__ list, const int nlist, double *__restrict__ gscratch) {
     if (ctl->done) return;
     extern __shared__ double smem[];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int team = wid >> 1, side = wid & 1, bar = 1 + team;
     double *__restrict__ R = smem;                                   // R[m] = 1/m, m = 1..rlen-1
-    double *__restrict__ S = smem + rlen + (size_t)team * stride;
-    volatile int *ti = reinterpret_cast<volatile int *>(S + (stride - 8)); // team mailbox: 16 ints
+    double *__restrict__ S = GS ? gscratch + ((size_t)blockIdx.x * (blockDim.x >> 6) + team) * (size_t)stride
+                                : smem + rlen + (size_t)team * stride;
+    volatile int *ti = reinterpret_cast<volatile int *>(GS ? smem + rlen + 8 * team : S + (stride - 8)); // team mailbox: 16 ints
     for (int m = threadIdx.x; m < rlen; m += blockDim.x) R[m] = m ? 1.0 / (double)m : 0.0;
     __syncthreads();
     const double alpha = ctl->alpha;
@@ -623,21 +626,29 @@ GflSolver::GflSolver(int nbins, unsigned maxdiag, cudaStream_t stream) : nbins_(
         prox_stride_ = lmax + 2 + 8;   // S[0..L], one spare slot, 16-int team mailbox
         prox_rlen_ = lmax + 1;
         const int64_t words = (int64_t)smem_max / 8;
-        // the full reciprocal table while two chains still fit beside it; else a 2048-entry table and in-place
-        // quotients beyond it (LONG mode: chains up to ~27 000 cells, one team per SM)
-        constexpr int RT_SHORT = 2048;
-        prox_long_ = (words - prox_rlen_) / prox_stride_ < 2 && prox_rlen_ > RT_SHORT;
-        if (const char *e = std::getenv("FB_PROX_RTAB")) { // test aid: force LONG mode with a table of this size
+        // Short chains: prefix sums and the full reciprocal table in shared memory, ten teams per SM. When fewer than
+        // PROX_GS_BELOW teams would fit, the prefix sums move to global scratch (GS) and shared memory keeps the table;
+        // beyond ~28 000 cells the table is cut and the quotient computed in place past its end (LONG).
+        constexpr int PROX_GS_BELOW = PROX_MAX_TEAMS;
+        int64_t fit = (words - prox_rlen_) / prox_stride_;
+        prox_gs_ = fit < PROX_GS_BELOW;
+        if (const char *e = std::getenv("FB_PROX_GS")) prox_gs_ = std::atoi(e) != 0 || fit < 1;
+        prox_long_ = false;
+        if (prox_gs_) {
+            const int64_t cap = words - 8 * PROX_MAX_TEAMS - 8;
+            if (prox_rlen_ > cap) { prox_rlen_ = (int)cap; prox_long_ = true; }
+        }
+        if (const char *e = std::getenv("FB_PROX_RTAB")) { // test aid: a table of this size (forces GS + LONG)
             const int v = std::atoi(e);
-            if (v >= 2 && v < prox_rlen_) { prox_long_ = true; prox_rlen_ = v; }
-        } else if (prox_long_) prox_rlen_ = RT_SHORT;
-        prox_warps_ = std::min<int64_t>(PROX_MAX_TEAMS, (words - prox_rlen_) / (int64_t)prox_stride_);
-        if (prox_warps_ < 1) throw ArgError("chains longer than 26990 cells are not supported by this build of the fused-lasso prox");
+            if (v >= 2 && v < prox_rlen_) { prox_long_ = true; prox_gs_ = true; prox_rlen_ = v; }
+        }
+        prox_warps_ = prox_gs_ ? PROX_MAX_TEAMS : std::min<int64_t>(PROX_MAX_TEAMS, fit);
         prox_warps_ = std::min(prox_warps_, std::max(1, (g_.nchains() + n_sm_ - 1) / n_sm_));
-        prox_smem_ = ((size_t)prox_warps_ * prox_stride_ + prox_rlen_) * 8;
-        if (prox_long_) FB_CUDA(cudaFuncSetAttribute(k_prox<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)prox_smem_));
-        else FB_CUDA(cudaFuncSetAttribute(k_prox<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)prox_smem_));
+        prox_smem_ = prox_gs_ ? ((size_t)prox_rlen_ + 8 * prox_warps_ + 8) * 8 : ((size_t)prox_warps_ * prox_stride_ + prox_rlen_) * 8;
+        const void *fn = prox_long_ ? (const void *)k_prox<true, true> : prox_gs_ ? (const void *)k_prox<false, true> : (const void *)k_prox<false, false>;
+        FB_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)prox_smem_));
         prox_grid_ = std::min(n_sm_, (g_.nchains() + prox_warps_ - 1) / prox_warps_);
+        if (prox_gs_) gscratch_.alloc((size_t)prox_grid_ * prox_warps_ * prox_stride_);
     }
     ctl_.alloc(1);
     if (std::getenv("FB_PROX_TRACE")) { trace_.alloc(4 * (size_t)g_.nchains()); trace_.zero(); }
@@ -670,7 +681,7 @@ void GflSolver::setup_shard() {
     n_list_ = (int)list.size();
     chain_list_.alloc(std::max<size_t>(1, list.size()));
     if (n_list_) FB_CUDA(cudaMemcpy(chain_list_.p, list.data(), list.size() * sizeof(int), cudaMemcpyHostToDevice));
-    prox_grid_ = std::max(1, std::min(n_sm_, (n_list_ + prox_warps_ - 1) / prox_warps_));
+    prox_grid_ = std::max(1, std::min(prox_grid_, (n_list_ + prox_warps_ - 1) / prox_warps_));   // never above the scratch slots
     // regions
     auto line_cells = [&](int dir, int line, int x0, int x1) -> int {
         int lo, hi;
@@ -775,12 +786,13 @@ void GflSolver::launch_iteration(const double *y, const double *w, bool in_graph
     dim3 tb(TILE, 8), tg((g_.n + TILE - 1) / TILE, (g_.n + TILE - 1) / TILE);
     k_beta<<<tg, tb, 0, st_>>>(g_, ctl_.p, y, w, zr_.p, ur_.p, zc_.p, uc_.p, beta_.p, betaT_.p, r0_, r1_, c0_, c1_);
     const int *list = sharded_ ? chain_list_.p : nullptr;
-    if (prox_long_)
-        k_prox<true><<<prox_grid_, 64 * prox_warps_, prox_smem_, st_>>>(g_, ctl_.p, beta_.p, betaT_.p, zr_.p, ur_.p, zc_.p, uc_.p,
-                                                                       partials_.p, prox_stride_, prox_rlen_, trace_.p, list, n_list_);
-    else
-        k_prox<false><<<prox_grid_, 64 * prox_warps_, prox_smem_, st_>>>(g_, ctl_.p, beta_.p, betaT_.p, zr_.p, ur_.p, zc_.p, uc_.p,
-                                                                        partials_.p, prox_stride_, prox_rlen_, trace_.p, list, n_list_);
+#define FB_PROX_LAUNCH(LONG_, GS_)                                                                                              \
+    k_prox<LONG_, GS_><<<prox_grid_, 64 * prox_warps_, prox_smem_, st_>>>(g_, ctl_.p, beta_.p, betaT_.p, zr_.p, ur_.p, zc_.p, uc_.p,  \
+                                                                         partials_.p, prox_stride_, prox_rlen_, trace_.p, list, n_list_, gscratch_.p)
+    if (prox_long_) FB_PROX_LAUNCH(true, true);
+    else if (prox_gs_) FB_PROX_LAUNCH(false, true);
+    else FB_PROX_LAUNCH(false, false);
+#undef FB_PROX_LAUNCH
     // sharded: the residual sums of every chain on every rank (exactly one rank contributes a non-zero term per
     // slot, so the sum is exact and k_ctl reduces the same numbers in the same order everywhere)
     if (sharded_) Comm::get().allreduce_sum(partials_.p, partials_all_.p, 2 * (size_t)n_partials_, st_);

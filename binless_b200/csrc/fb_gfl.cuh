@@ -127,6 +127,8 @@ private:
     int n_sm_ = 148, prox_warps_ = 1, prox_grid_ = 1, prox_stride_ = 0, prox_rlen_ = 0;
     size_t prox_smem_ = 0;
     bool prox_long_ = false;           // reciprocal table shorter than the longest chain
+    bool prox_gs_ = false;             // prefix sums of the chains in global scratch instead of shared memory
+    DevBuf<double> gscratch_;
     cudaEvent_t ev0_, ev1_;
     // the whole ADMM loop as ONE graph launch: a WHILE conditional node whose body is one iteration, the condition
     // set on the device by k_ctl (no host polling, no launches queued past convergence)

@@ -22,7 +22,8 @@ def run(ms):
     rc = gpu._gfl_solve(n, 0, _dp(y), _dp(w), 2.5, 1e-12, ms, 0, C.byref(st), None)
     gpu._check(rc, None)
     return time.time() - t, st.steps, beta
-ta, sa, _ = run(2)             # 1 iteration: upload / allocation / download overhead
+run(2)                         # warm-up: allocations
+ta, sa, _ = run(2)             # 1 iteration: upload / download overhead
 tb, sb, beta = run(maxsteps)
 per = (tb - ta) / max(1, (sb - sa))
 print(f"steps {sa}->{sb}: {ta:.3f}s -> {tb:.3f}s  => {per*1e3:.3f} ms per ADMM iteration, "
