@@ -667,6 +667,7 @@ GflSolver::GflSolver(int nbins, unsigned maxdiag, cudaStream_t stream) : nbins_(
 void GflSolver::setup_shard() {
     Comm &cm = Comm::get();
     sharded_ = true; rank_ = cm.rank(); world_ = cm.world();
+    shard_timing_ = std::getenv("FB_SHARD_TIMING") != nullptr;
     row_begin_.resize(world_ + 1); col_begin_.resize(world_ + 1);
     shard_plan(g_.n, g_.md, world_, row_begin_.data(), col_begin_.data());
     r0_ = row_begin_[rank_]; r1_ = row_begin_[rank_ + 1];
@@ -729,12 +730,24 @@ void GflSolver::setup_shard() {
     partials_all_.alloc(partials_.n);
 }
 
+void GflSolver::tmark(int k) {
+    if (!shard_timing_) return;
+    if (tev_.empty()) { tev_.resize(8); for (auto &e : tev_) cudaEventCreate(&e); }
+    cudaEventRecord(tev_[k], st_);
+}
+void GflSolver::tflush() { // after a stream synchronisation: add the phases of the LAST iteration (a sample per poll batch)
+    if (!shard_timing_ || tev_.empty()) return;
+    for (int k = 0; k < 7; ++k) { float ms = 0.f; if (cudaEventElapsedTime(&ms, tev_[k], tev_[k + 1]) == cudaSuccess) tacc_[k] += ms; }
+    ++tcount_;
+}
+
 // z - u of the crossing cells, both directions, to and from every peer
 void GflSolver::exchange(bool zero_u) {
     Comm &cm = Comm::get();
     dim3 grid((unsigned)std::min(max_lines_, 4096), (unsigned)(world_ - 1));
     k_exchange<0, true><<<grid, 256, 0, st_>>>(g_, ctl_.p, send_regs_.p, send_lineoff_.p, zr_.p, ur_.p, send_buf_.p, 0);
     k_exchange<1, true><<<grid, 256, 0, st_>>>(g_, ctl_.p, send_regs_.p, send_lineoff_.p, zc_.p, uc_.p, send_buf_.p, 0);
+    tmark(5);
     cm.group_start();
     for (int p = 0; p < world_; ++p) {
         if (p == rank_) continue;
@@ -742,9 +755,11 @@ void GflSolver::exchange(bool zero_u) {
         if (recv_cnt_[p]) cm.recv(recv_buf_.p + recv_off_[p], (size_t)recv_cnt_[p], p, st_);
     }
     cm.group_end();
+    tmark(6);
     k_exchange<0, false><<<grid, 256, 0, st_>>>(g_, ctl_.p, recv_regs_.p, recv_lineoff_.p, zr_.p, ur_.p, recv_buf_.p, zero_u ? 1 : 0);
     k_exchange<1, false><<<grid, 256, 0, st_>>>(g_, ctl_.p, recv_regs_.p, recv_lineoff_.p, zc_.p, uc_.p, recv_buf_.p, zero_u ? 1 : 0);
     kernel_launches += 4;
+    tmark(7);
 }
 
 // every rank ends with the whole array: the row blocks (row-major array) or column blocks (column-major array)
@@ -769,6 +784,13 @@ void GflSolver::allgather_cols(double *a) {
 
 GflSolver::~GflSolver() {
     cudaStreamSynchronize(st_); // buffers go back to the block cache only when nothing uses them any more
+    if (shard_timing_ && tcount_) {
+        static const char *nm[7] = {"k_beta", "k_prox", "allreduce", "k_ctl", "pack", "send/recv", "unpack"};
+        std::fprintf(stderr, "[fb shard timing] rank %d n=%d, mean over %d sampled iterations (ms):", rank_, g_.n, tcount_);
+        for (int k = 0; k < 7; ++k) std::fprintf(stderr, " %s %.3f", nm[k], tacc_[k] / tcount_);
+        std::fprintf(stderr, "\n");
+    }
+    for (auto &e : tev_) cudaEventDestroy(e);
     if (graph_exec_) cudaGraphExecDestroy(graph_exec_);
     if (graph_) cudaGraphDestroy(graph_);
     if (h_ctl_) BlockCache::host().put(h_ctl_, sizeof(GflCtl));
@@ -784,7 +806,9 @@ void GflSolver::reset() {
 
 void GflSolver::launch_iteration(const double *y, const double *w, bool in_graph) {
     dim3 tb(TILE, 8), tg((g_.n + TILE - 1) / TILE, (g_.n + TILE - 1) / TILE);
+    tmark(0);
     k_beta<<<tg, tb, 0, st_>>>(g_, ctl_.p, y, w, zr_.p, ur_.p, zc_.p, uc_.p, beta_.p, betaT_.p, r0_, r1_, c0_, c1_);
+    tmark(1);
     const int *list = sharded_ ? chain_list_.p : nullptr;
 #define FB_PROX_LAUNCH(LONG_, GS_)                                                                                              \
     k_prox<LONG_, GS_><<<prox_grid_, 64 * prox_warps_, prox_smem_, st_>>>(g_, ctl_.p, beta_.p, betaT_.p, zr_.p, ur_.p, zc_.p, uc_.p,  \
@@ -795,10 +819,13 @@ void GflSolver::launch_iteration(const double *y, const double *w, bool in_graph
 #undef FB_PROX_LAUNCH
     // sharded: the residual sums of every chain on every rank (exactly one rank contributes a non-zero term per
     // slot, so the sum is exact and k_ctl reduces the same numbers in the same order everywhere)
+    tmark(2);
     if (sharded_) Comm::get().allreduce_sum(partials_.p, partials_all_.p, 2 * (size_t)n_partials_, st_);
+    tmark(3);
     const double *parts = sharded_ ? partials_all_.p : partials_.p;
     if (in_graph) k_ctl<true><<<1, CTL_THREADS, 0, st_>>>(ctl_.p, parts, n_partials_, g_.ncells, 2 * g_.ncells - 2, cond_);
     else k_ctl<false><<<1, CTL_THREADS, 0, st_>>>(ctl_.p, parts, n_partials_, g_.ncells, 2 * g_.ncells - 2, cond_);
+    tmark(4);
     if (sharded_) exchange(false);
 }
 
@@ -863,6 +890,7 @@ int GflSolver::optimize(const double *d_y_tri, const double *d_w_tri, double lam
         FB_LAUNCH_CHECK();
         FB_CUDA(cudaMemcpyAsync(h_ctl_, ctl_.p, sizeof(GflCtl), cudaMemcpyDeviceToHost, st_));
         FB_CUDA(cudaStreamSynchronize(st_));
+        if (!h_ctl_->done) tflush();
         done = h_ctl_->done != 0;
     }
     if (!c.done) {

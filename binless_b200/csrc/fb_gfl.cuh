@@ -115,6 +115,13 @@ private:
     DevBuf<int64_t> send_lineoff_, recv_lineoff_;
     DevBuf<double> send_buf_, recv_buf_;
     int max_lines_ = 1;
+    // FB_SHARD_TIMING development aid: device time per phase of the sharded iteration
+    bool shard_timing_ = false;
+    std::vector<cudaEvent_t> tev_;
+    double tacc_[8] = {};
+    int tcount_ = 0;
+    void tmark(int k);
+    void tflush();
     void setup_shard();
     void exchange(bool zero_u);
     void allgather_rows(double *rm_array);
