@@ -18,7 +18,7 @@ import os
 from ._abi import FastBinlessError, FastBinlessLib
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libfastbinless_cuda.so")
+LIB_PATH = os.environ.get("FB_LIB") or os.path.join(_HERE, "libfastbinless_cuda.so")   # FB_LIB: development builds
 _lib = None
 
 

@@ -29,7 +29,10 @@ namespace {
 constexpr int TILE = 32;
 constexpr int CTL_THREADS = 1024;
 constexpr int POLL_BATCH = 8;
-constexpr int PROX_MAX_TEAMS = 10;    // two warps per chain; 704 threads leave 88 registers per thread
+constexpr int PROX_MAX_TEAMS = 10;    // two warps per chain; 640 threads leave 96 registers per thread (instruction bound:
+                                      // more teams with fewer registers are slower at 2400 bins, 261 -> 299 us with 12)
+constexpr int PROX_GS_TEAMS = 15;     // chains in global scratch are latency bound: 15 teams (64 registers, named barriers
+                                      // 1..15) are faster there (12 000 bins: 17.4 -> 13.3 ms per iteration)
 constexpr unsigned FULL = 0xffffffffu;
 
 // --------------------------------------------------------------------------
@@ -357,7 +360,7 @@ __device__ __forceinline__ int taut_string_team(double *__restrict__ S, volatile
 // GS: the prefix sums of a chain live in a per-team slot of global scratch (L1/L2 resident) instead of shared memory,
 // which then holds only the reciprocal table: ten teams per SM whatever the chain length.
 template <bool LONG, bool GS>
-__global__ void __launch_bounds__(64 * PROX_MAX_TEAMS, 1)
+__global__ void __launch_bounds__(64 * (GS ? PROX_GS_TEAMS : PROX_MAX_TEAMS), 1)
 k_prox(Grid g, GflCtl *__restrict__ ctl, const double *__restrict__ beta, const double *__restrict__ betaT,
        double *__restrict__ zr, double *__restrict__ ur, double *__restrict__ zc, double *__restrict__ uc,
        double *__restrict__ partials, int stride, int rlen, long long *__restrict__ trace,
@@ -629,20 +632,20 @@ GflSolver::GflSolver(int nbins, unsigned maxdiag, cudaStream_t stream) : nbins_(
         // Short chains: prefix sums and the full reciprocal table in shared memory, ten teams per SM. When fewer than
         // PROX_GS_BELOW teams would fit, the prefix sums move to global scratch (GS) and shared memory keeps the table;
         // beyond ~28 000 cells the table is cut and the quotient computed in place past its end (LONG).
-        constexpr int PROX_GS_BELOW = PROX_MAX_TEAMS;
+        constexpr int PROX_GS_BELOW = 6;   // measured: 3000 bins (8 teams fit) is faster in shared memory, 6000 (3 fit) in scratch
         int64_t fit = (words - prox_rlen_) / prox_stride_;
         prox_gs_ = fit < PROX_GS_BELOW;
         if (const char *e = std::getenv("FB_PROX_GS")) prox_gs_ = std::atoi(e) != 0 || fit < 1;
         prox_long_ = false;
         if (prox_gs_) {
-            const int64_t cap = words - 8 * PROX_MAX_TEAMS - 8;
+            const int64_t cap = words - 8 * PROX_GS_TEAMS - 8;
             if (prox_rlen_ > cap) { prox_rlen_ = (int)cap; prox_long_ = true; }
         }
         if (const char *e = std::getenv("FB_PROX_RTAB")) { // test aid: a table of this size (forces GS + LONG)
             const int v = std::atoi(e);
             if (v >= 2 && v < prox_rlen_) { prox_long_ = true; prox_gs_ = true; prox_rlen_ = v; }
         }
-        prox_warps_ = prox_gs_ ? PROX_MAX_TEAMS : std::min<int64_t>(PROX_MAX_TEAMS, fit);
+        prox_warps_ = prox_gs_ ? PROX_GS_TEAMS : std::min<int64_t>(PROX_MAX_TEAMS, fit);
         prox_warps_ = std::min(prox_warps_, std::max(1, (g_.nchains() + n_sm_ - 1) / n_sm_));
         prox_smem_ = prox_gs_ ? ((size_t)prox_rlen_ + 8 * prox_warps_ + 8) * 8 : ((size_t)prox_warps_ * prox_stride_ + prox_rlen_) * 8;
         const void *fn = prox_long_ ? (const void *)k_prox<true, true> : prox_gs_ ? (const void *)k_prox<false, true> : (const void *)k_prox<false, false>;
