@@ -399,13 +399,23 @@ k_prox(Grid g, GflCtl *__restrict__ ctl, const double *__restrict__ beta, const 
         double c = 0.0;
         if (!copy && side) c = __ldcg(B) + __ldcg(U);
         // stage v = beta + u at S[k+1], coalesced, 8 loads per array in flight
+        int ps = lo_;
 #pragma unroll 1
-        for (int p = lo_; p < hi_; p += 256) {
+        for (; ps + 256 <= hi_; ps += 256) {   // whole batches: no predicates, one address per array
+            const double *__restrict__ bp = B + ps + lane, *__restrict__ up = U + ps + lane;
+            double *__restrict__ sp = S + ps + lane + 1;
             double vb[8], vu[8];
 #pragma unroll
-            for (int b = 0; b < 8; ++b) { const int k = p + 32 * b + lane; vb[b] = k < hi_ ? __ldcg(B + k) : 0.0; vu[b] = k < hi_ ? __ldcg(U + k) : 0.0; }
+            for (int b = 0; b < 8; ++b) { vb[b] = __ldcg(bp + 32 * b); vu[b] = __ldcg(up + 32 * b); }
 #pragma unroll
-            for (int b = 0; b < 8; ++b) { const int k = p + 32 * b + lane; if (k < hi_) S[k + 1] = vb[b] + vu[b]; }
+            for (int b = 0; b < 8; ++b) sp[32 * b] = vb[b] + vu[b];
+        }
+        if (ps < hi_) {
+            double vb[8], vu[8];
+#pragma unroll
+            for (int b = 0; b < 8; ++b) { const int k = ps + 32 * b + lane; vb[b] = k < hi_ ? __ldcg(B + k) : 0.0; vu[b] = k < hi_ ? __ldcg(U + k) : 0.0; }
+#pragma unroll
+            for (int b = 0; b < 8; ++b) { const int k = ps + 32 * b + lane; if (k < hi_) S[k + 1] = vb[b] + vu[b]; }
         }
         __syncwarp();
         int split = 0; // cell i of the solution at S[i] for i < split, else at S[i + 1]
@@ -413,9 +423,22 @@ k_prox(Grid g, GflCtl *__restrict__ ctl, const double *__restrict__ beta, const 
             if (!side) c = S[1];
             // in-place prefix sums of (v_i - c) over this warp's half: lane-local runs of PB, one warp scan per 32*PB
             double carry = 0.0;
+            int pp = lo_;
 #pragma unroll 1
-            for (int p = lo_; p < hi_; p += PW) {
-                const int kb = p + lane * PB;
+            for (; pp + PW <= hi_; pp += PW) {     // whole blocks: no predicates
+                double *__restrict__ sp = S + pp + lane * PB + 1;
+                double t[PB];
+                double run = 0.0;
+#pragma unroll
+                for (int b = 0; b < PB; ++b) { run += sp[b] - c; t[b] = run; }
+                const double incl = scan_sum_incl(run, lane);
+                const double off = (incl - run) + carry;
+#pragma unroll
+                for (int b = 0; b < PB; ++b) sp[b] = t[b] + off;
+                carry += __shfl_sync(FULL, incl, 31);
+            }
+            if (pp < hi_) {
+                const int kb = pp + lane * PB;
                 double t[PB];
                 double run = 0.0;
 #pragma unroll
@@ -424,7 +447,6 @@ k_prox(Grid g, GflCtl *__restrict__ ctl, const double *__restrict__ beta, const 
                 const double off = (incl - run) + carry;
 #pragma unroll
                 for (int b = 0; b < PB; ++b) { const int k = kb + b; if (k < hi_) S[k + 1] = t[b] + off; }
-                carry += __shfl_sync(FULL, incl, 31);
             }
             if (!side && lane == 0) S[0] = 0.0;
             team_sync(bar);
@@ -448,17 +470,37 @@ k_prox(Grid g, GflCtl *__restrict__ ctl, const double *__restrict__ beta, const 
         }
         // u += beta - z, residual sums (gfl_graph_fl.c:306-365)
         double ap = 0.0, ad = 0.0;
+        int po = lo_;
 #pragma unroll 1
-        for (int p = lo_; p < hi_; p += 256) {
+        for (; po + 256 <= hi_; po += 256) {   // whole batches
+            const double *__restrict__ bp = B + po + lane;
+            double *__restrict__ up = U + po + lane, *__restrict__ zp = Z + po + lane;
+            const int k0 = po + lane;
+            double b8[8], u8[8], z8[8];
+#pragma unroll
+            for (int b = 0; b < 8; ++b) { b8[b] = __ldcg(bp + 32 * b); u8[b] = __ldcg(up + 32 * b); z8[b] = __ldcg(zp + 32 * b); }
+#pragma unroll
+            for (int b = 0; b < 8; ++b) {
+                const int k = k0 + 32 * b;
+                const double z = S[k < split ? k : k + 1];
+                const double r = b8[b] - z;
+                __stcg(up + 32 * b, u8[b] + r);
+                __stcg(zp + 32 * b, z);
+                ap += r * r;
+                const double dd = alpha * (z - z8[b]);
+                ad += dd * dd;
+            }
+        }
+        if (po < hi_) {
             double b8[8], u8[8], z8[8];
 #pragma unroll
             for (int b = 0; b < 8; ++b) {
-                const int k = p + 32 * b + lane;
+                const int k = po + 32 * b + lane;
                 b8[b] = k < hi_ ? __ldcg(B + k) : 0.0; u8[b] = k < hi_ ? __ldcg(U + k) : 0.0; z8[b] = k < hi_ ? __ldcg(Z + k) : 0.0;
             }
 #pragma unroll
             for (int b = 0; b < 8; ++b) {
-                const int k = p + 32 * b + lane;
+                const int k = po + 32 * b + lane;
                 if (k < hi_) {
                     const double z = S[k < split ? k : k + 1];
                     const double r = b8[b] - z;
