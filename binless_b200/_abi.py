@@ -71,7 +71,8 @@ class fb_gfl_state(C.Structure):
 
 ENTRY_POINTS = ["create", "destroy", "last_error", "run_signal", "restore", "run_difference",
                 "eval_cv", "sweep_lambda", "gfl_solve", "set_interrupt_cb", "kernel_launches", "release_cached_memory",
-                "comm_unique_id", "comm_init", "comm_destroy", "comm_rank", "comm_world", "shard_plan"]
+                "comm_unique_id", "comm_init", "comm_destroy", "comm_rank", "comm_world", "shard_plan",
+                "create_binned", "get_mat", "mat_rows"]
 
 
 def _dp(a):
@@ -94,6 +95,13 @@ class FastBinlessError(RuntimeError):
     def __init__(self, code, msg):
         super().__init__(msg)
         self.code = code
+
+
+class fb_reads(C.Structure):
+    _fields_ = [("ndatasets", C.c_int), ("resolution", C.c_int),
+                ("ncuts", C.c_int64), ("cut_name", c_ip), ("cut_pos", c_ip),
+                ("nreads", C.c_int64), ("rd_name", c_ip), ("rd_pos1", c_ip), ("rd_pos2", c_ip),
+                ("contact_close", c_ip), ("contact_far", c_ip), ("contact_up", c_ip), ("contact_down", c_ip)]
 
 
 class FastBinlessLib:
@@ -136,6 +144,11 @@ class FastBinlessLib:
         self._gfl_solve.argtypes = [C.c_int, C.c_uint, c_dp, c_dp, C.c_double, C.c_double, C.c_int, C.c_int,
                                     C.POINTER(fb_gfl_state), c_dp]
         self._gfl_solve.restype = C.c_int
+        self._create_binned = f("create_binned")
+        self._create_binned.argtypes = [C.POINTER(fb_reads), C.POINTER(C.c_int), C.POINTER(C.c_void_p)]; self._create_binned.restype = C.c_int
+        self._get_mat = f("get_mat")
+        self._get_mat.argtypes = [C.c_void_p, c_ip, c_ip, c_ip, c_ip, c_ip, c_dp, c_ip, c_ip]; self._get_mat.restype = C.c_int
+        self._mat_rows = f("mat_rows"); self._mat_rows.argtypes = [C.c_void_p]; self._mat_rows.restype = C.c_int64
         self._comm_unique_id = f("comm_unique_id"); self._comm_unique_id.argtypes = [C.c_void_p]; self._comm_unique_id.restype = C.c_int
         self._comm_init = f("comm_init"); self._comm_init.argtypes = [C.c_int, C.c_int, C.c_void_p]; self._comm_init.restype = C.c_int
         self._comm_destroy = f("comm_destroy"); self._comm_destroy.argtypes = []; self._comm_destroy.restype = C.c_int
@@ -177,6 +190,23 @@ class FastBinlessLib:
                       csv_out=(csv_out or "").encode(), maxdiag=int(maxdiag), verbose=int(bool(verbose)))
         p._keep = (lam2a, lam1a)
         return p
+
+    def create_binned(self, reads, resolution, ndatasets):
+        """bin_data() of a CSnorm-like object: ``reads`` holds cut_name, cut_pos (obj@biases) and rd_name, rd_pos1,
+        rd_pos2, contact_close / far / up / down (obj@counts). Returns a Handle whose matrix was built by the library."""
+        a = {k: _i32(reads[k]) for k in ("cut_name", "cut_pos", "rd_name", "rd_pos1", "rd_pos2", "contact_close",
+                                         "contact_far", "contact_up", "contact_down")}
+        r = fb_reads(ndatasets=int(ndatasets), resolution=int(resolution), ncuts=a["cut_pos"].size, nreads=a["rd_pos1"].size,
+                     **{k: _ip(v) for k, v in a.items()})
+        h = C.c_void_p(); nb = C.c_int(0)
+        self._check(self._create_binned(C.byref(r), C.byref(nb), C.byref(h)), None)
+        N = int(self._mat_rows(h))
+        cols = {"distance": np.empty(N)}
+        for k in ("name", "bin1", "pos1", "bin2", "pos2", "observed", "nobs"):
+            cols[k] = np.empty(N, dtype=np.int32)
+        self._check(self._get_mat(h, _ip(cols["name"]), _ip(cols["bin1"]), _ip(cols["pos1"]), _ip(cols["bin2"]), _ip(cols["pos2"]),
+                                  _dp(cols["distance"]), _ip(cols["observed"]), _ip(cols["nobs"])), None)
+        return Handle(self, h, cols, nb.value)
 
     def create(self, mat, nbins):
         cols = {}

@@ -5,7 +5,11 @@
 #include "fb_comm.cuh"
 #include <string>
 
-struct fb_handle { fb::Model m; fb_handle(int nbins, const fb_mat *mat) : m(nbins, mat) {} };
+struct fb_handle {
+    fb::Model m;
+    fb_handle(int nbins, const fb_mat *mat) : m(nbins, mat) {}
+    fb_handle(const fb_reads *reads, int *nbins) : m(reads, nbins) {}
+};
 
 namespace {
 template <typename F>
@@ -29,6 +33,18 @@ FB_API int fb_create(int nbins, const fb_mat *mat, fb_handle **out) {
     *out = nullptr;
     return guarded(fb::g_last_error, [&] { *out = new fb_handle(nbins, mat); });
 }
+
+FB_API int fb_create_binned(const fb_reads *reads, int *nbins, fb_handle **out) {
+    if (!out) { fb::g_last_error = "null handle pointer"; return FB_ERR_ARG; }
+    *out = nullptr;
+    return guarded(fb::g_last_error, [&] { *out = new fb_handle(reads, nbins); });
+}
+FB_API int fb_get_mat(fb_handle *h, int32_t *name, int32_t *bin1, int32_t *pos1, int32_t *bin2, int32_t *pos2,
+                      double *distance, int32_t *observed, int32_t *nobs) {
+    if (!h) { fb::g_last_error = "null handle"; return FB_ERR_ARG; }
+    return guarded(h->m.err, [&] { h->m.get_mat(name, bin1, pos1, bin2, pos2, distance, observed, nobs); });
+}
+FB_API int64_t fb_mat_rows(const fb_handle *h) { return h ? h->m.rows() : 0; }
 
 FB_API void fb_destroy(fb_handle *h) { delete h; }
 

@@ -106,6 +106,31 @@ Model::Model(int nbins, const fb_mat *mat) {
     ingest(nbins, mat);
 }
 
+Model::Model(const fb_reads *reads, int *nbins_out) {
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+        throw CudaError("no CUDA device available (there is no CPU fallback)");
+    FB_CUDA(cudaStreamCreateWithFlags(&st_, cudaStreamNonBlocking));
+    FB_CUDA(cudaEventCreate(&ev0_));
+    FB_CUDA(cudaEventCreate(&ev1_));
+    ingest_reads(reads, nbins_out);
+}
+
+// the per-handle work buffers that do not depend on how the matrix arrived
+void Model::alloc_work() {
+    const int64_t n = t_.n, D = t_.D, N = D * t_.ncells;
+    phi_.alloc(N); phi_new_.alloc(N); phihat_.alloc(N); wgt_.alloc(N);
+    phi_.zero(st_); phihat_.zero(st_); wgt_.zero(st_);
+    tab_.alloc(2 * (size_t)n + D); tab_old_.alloc(2 * (size_t)n + D);
+    tab_h_.alloc(2 * (size_t)n + D);
+    items_.alloc(2 * (size_t)std::max<int64_t>(n, D)); items_h_.alloc(2 * (size_t)std::max<int64_t>(n, D));
+    prec_h_.alloc(4);
+    part_.alloc(leg_part_doubles(t_));
+    scratch_.alloc(4096);
+    keys_.alloc((size_t)(2 * n + 1) * D + 8);
+    FB_CUDA(cudaStreamSynchronize(st_));
+}
+
 Model::~Model() {
     if (st_) cudaStreamSynchronize(st_); // buffers go back to the block cache only when nothing uses them any more
     if (ev0_) cudaEventDestroy(ev0_);
@@ -188,15 +213,17 @@ void Model::ingest(int nbins, const fb_mat *m) {
     });
     FB_CUDA(cudaMemcpyAsync(obs_.p, m->observed, N * sizeof(int32_t), cudaMemcpyHostToDevice, st_));
     FB_CUDA(cudaMemcpyAsync(nobs_.p, m->nobs, N * sizeof(int32_t), cudaMemcpyHostToDevice, st_));
-    phi_.alloc(N); phi_new_.alloc(N); phihat_.alloc(N); wgt_.alloc(N);
-    phi_.zero(st_); phihat_.zero(st_); wgt_.zero(st_);
-    tab_.alloc(2 * (size_t)n + D); tab_old_.alloc(2 * (size_t)n + D);
-    tab_h_.alloc(2 * (size_t)n + D);
-    items_.alloc(2 * (size_t)std::max<int64_t>(n, D)); items_h_.alloc(2 * (size_t)std::max<int64_t>(n, D));
-    prec_h_.alloc(4);
-    part_.alloc(leg_part_doubles(t_));
-    scratch_.alloc(4096);
-    keys_.alloc((size_t)(2 * n + 1) * D + 8);
+    { // same buffers as alloc_work(), without its synchronisation: the validation below overlaps the uploads
+        phi_.alloc(N); phi_new_.alloc(N); phihat_.alloc(N); wgt_.alloc(N);
+        phi_.zero(st_); phihat_.zero(st_); wgt_.zero(st_);
+        tab_.alloc(2 * (size_t)n + D); tab_old_.alloc(2 * (size_t)n + D);
+        tab_h_.alloc(2 * (size_t)n + D);
+        items_.alloc(2 * (size_t)std::max<int64_t>(n, D)); items_h_.alloc(2 * (size_t)std::max<int64_t>(n, D));
+        prec_h_.alloc(4);
+        part_.alloc(leg_part_doubles(t_));
+        scratch_.alloc(4096);
+        keys_.alloc((size_t)(2 * n + 1) * D + 8);
+    }
     const char *e = checks.get();
     FB_CUDA(cudaStreamSynchronize(st_));
     if (e) throw ArgError(e);

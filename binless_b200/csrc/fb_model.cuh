@@ -35,6 +35,10 @@ struct PinBuf {
 class Model {
 public:
     Model(int nbins, const fb_mat *mat);
+    Model(const fb_reads *reads, int *nbins_out);     // bin_data() on the device (fb_bin.cu)
+    void get_mat(int32_t *name, int32_t *bin1, int32_t *pos1, int32_t *bin2, int32_t *pos2, double *distance,
+                 int32_t *observed, int32_t *nobs);
+    int64_t rows() const { return (int64_t)t_.D * t_.ncells; }
     ~Model();
     void run_signal(const fb_params *p, fb_signal_out *out);
     void restore(const double *log_signal, const fb_mean_state *biases, const fb_gam_state *decay,
@@ -74,6 +78,8 @@ private:
 
     LegTables tables(const DevBuf<double> &b) const { return LegTables{b.p, b.p + t_.n, b.p + 2 * (size_t)t_.n}; }
     void ingest(int nbins, const fb_mat *mat);
+    void ingest_reads(const fb_reads *reads, int *nbins_out);
+    void alloc_work();
     void build_legs(double tol_val, unsigned free_decay);
     void upload_tables();
     // runs one leg pass and returns the per-bin sums (a, b) on the host

@@ -135,6 +135,27 @@ typedef struct {
     int32_t *patchno;
 } fb_cv_out;
 
+/* Input side: bin_data() for a CSnorm object, /root/reference/binless/R/preprocess.R:104-148
+ * with add_bin_bounds_and_distance(), R/common.R:115-132, done on the device so that the dense matrix never exists on
+ * the host. `cut_*` is obj@biases (one row per cut site: dataset 1..ndatasets and position), `rd_*` is obj@counts (one
+ * row per pair of cut sites with its four contact counts). Bins: borders b0 + k*resolution from b0 = min(pos) - 1
+ * while <= max(pos) + 1, the last incomplete bin discarded, intervals closed on the left, the last one also on the right;
+ * nobs = 4 * cuts(bin1) * cuts(bin2), halved (integer) on the diagonal; observed = sum of the four counts; a cell without
+ * a read row gets observed = nobs = 0 (a row whose four counts are zero keeps nobs); observed[(1, nbins)] += 1 in every dataset; pos = (begin + end) / 2 (integer),
+ * distance = begin2 - begin1 + resolution / 2. */
+typedef struct {
+    int ndatasets, resolution;
+    int64_t ncuts;  const int32_t *cut_name, *cut_pos;
+    int64_t nreads; const int32_t *rd_name, *rd_pos1, *rd_pos2;
+    const int32_t *contact_close, *contact_far, *contact_up, *contact_down;
+} fb_reads;
+/* the same handle fb_create returns, built from reads; *nbins receives the number of bins */
+FB_API int FB_NAME(create_binned)(const fb_reads *reads, int *nbins, fb_handle **out);
+/* the `mat` columns of a handle (what bin_data returns to R); arrays of N entries, any pointer may be NULL */
+FB_API int FB_NAME(get_mat)(fb_handle *h, int32_t *name, int32_t *bin1, int32_t *pos1, int32_t *bin2, int32_t *pos2,
+                            double *distance, int32_t *observed, int32_t *nobs);
+FB_API int64_t FB_NAME(mat_rows)(const fb_handle *h);
+
 /* FastDataCore constructor (FastData.ipp:3-26): validates and uploads. */
 FB_API int FB_NAME(create)(int nbins, const fb_mat *mat, fb_handle **out);
 FB_API void FB_NAME(destroy)(fb_handle *h);

@@ -1231,6 +1231,73 @@ FB_API int fbo_create(int nbins, const fb_mat *mat, fb_handle **out) {
     *out = h.release();
     return FB_OK;
 }
+/* bin_data() for a CSnorm object (R/preprocess.R:114-146) + add_bin_bounds_and_distance (R/common.R:115-132),
+ * restated with plain loops. */
+FB_API int fbo_create_binned(const fb_reads *r, int *nbins_out, fb_handle **out) {
+    if (!out || !r || !nbins_out) return FB_ERR_ARG;
+    *out = nullptr;
+    try {
+        if (r->ndatasets < 1 || r->resolution < 1 || r->ncuts < 1) throw ArgError("empty input");
+        int mn = r->cut_pos[0], mx = r->cut_pos[0];
+        for (int64_t k = 0; k < r->ncuts; ++k) { mn = std::min(mn, r->cut_pos[k]); mx = std::max(mx, r->cut_pos[k]); }
+        const int64_t res = r->resolution, b0 = (int64_t)mn - 1;
+        /* seq(min(pos)-1, max(pos)+1, resolution): borders b0 + k res <= mx + 1; one bin between consecutive borders */
+        const int64_t nb = ((int64_t)mx + 1 - b0) / res;
+        if (nb < 1) throw ArgError("no complete bin at this resolution");
+        const int64_t top = b0 + nb * res;
+        auto bin_of = [&](int pos) -> int64_t { /* cut(pos, borders, right=F, include.lowest=T): -1 is NA */
+            if (pos < b0 || pos > top) return -1;
+            if (pos == top) return nb - 1;
+            return ((int64_t)pos - b0) / res;
+        };
+        const int64_t D = r->ndatasets, nc = nb * (nb + 1) / 2, N = D * nc;
+        std::vector<int64_t> cuts(D * nb, 0);
+        for (int64_t k = 0; k < r->ncuts; ++k) {
+            const int64_t b = bin_of(r->cut_pos[k]);
+            if (b >= 0) cuts[(r->cut_name[k] - 1) * nb + b] += 1;
+        }
+        ivec name(N), bin1(N), bin2(N), pos1(N), pos2(N), observed(N, 0), nobs(N, 0);
+        std::vector<char> present(N, 0);   /* the cell has a row in poscounts (its counts may sum to zero) */
+        vec distance(N);
+        auto cell = [&](int64_t d, int64_t i, int64_t j) { return d * nc + i * nb - i * (i - 1) / 2 + (j - i); };
+        for (int64_t k = 0; k < r->nreads; ++k) {
+            const int64_t i = bin_of(r->rd_pos1[k]), j = bin_of(r->rd_pos2[k]);
+            if (i < 0 || j < 0 || i > j) continue;               /* NA bins and pairs below the diagonal match no cell */
+            const int64_t g = cell(r->rd_name[k] - 1, i, j);
+            observed[g] += r->contact_close[k] + r->contact_far[k] + r->contact_up[k] + r->contact_down[k];
+            present[g] = 1;
+        }
+        for (int64_t d = 0; d < D; ++d)
+            for (int64_t i = 0; i < nb; ++i)
+                for (int64_t j = i; j < nb; ++j) {
+                    const int64_t g = cell(d, i, j);
+                    name[g] = (int)d + 1; bin1[g] = (int)i + 1; bin2[g] = (int)j + 1;
+                    const int64_t beg1 = b0 + i * res, beg2 = b0 + j * res;
+                    pos1[g] = (int)((beg1 + beg1 + res) / 2); pos2[g] = (int)((beg2 + beg2 + res) / 2);
+                    distance[g] = (double)(beg2 - beg1) + (double)res / 2.0;
+                    int64_t no = 4 * cuts[d * nb + i] * cuts[d * nb + j];
+                    if (i == j) no /= 2;
+                    nobs[g] = !present[g] ? 0 : (int)std::min<int64_t>(no, INT32_MAX);   /* is.na(observed) -> both 0 */
+                }
+        for (int64_t d = 0; d < D; ++d) observed[cell(d, 0, nb - 1)] += 1;
+        fb_mat m{N, name.data(), bin1.data(), pos1.data(), bin2.data(), pos2.data(), observed.data(), nobs.data(), distance.data()};
+        std::unique_ptr<fb_handle> h(new fb_handle);
+        build_data(h->m.d, (int)nb, &m);
+        *nbins_out = (int)nb;
+        *out = h.release();
+        return FB_OK;
+    } catch (const std::exception &e) { g_create_error = e.what(); return FB_ERR_ARG; }
+}
+FB_API int64_t fbo_mat_rows(const fb_handle *h) { return h ? (int64_t)h->m.d.N : 0; }
+FB_API int fbo_get_mat(fb_handle *h, int32_t *name, int32_t *bin1, int32_t *pos1, int32_t *bin2, int32_t *pos2,
+                       double *distance, int32_t *observed, int32_t *nobs) {
+    if (!h) return FB_ERR_ARG;
+    const Data &d = h->m.d;
+    auto cp = [&](int32_t *dst, const ivec &src) { if (dst) std::copy(src.begin(), src.end(), dst); };
+    cp(name, d.name); cp(bin1, d.bin1); cp(pos1, d.pos1); cp(bin2, d.bin2); cp(pos2, d.pos2); cp(observed, d.observed); cp(nobs, d.nobs);
+    if (distance) std::copy(d.distance.begin(), d.distance.end(), distance);
+    return FB_OK;
+}
 FB_API void fbo_destroy(fb_handle *h) { delete h; }
 FB_API const char *fbo_last_error(const fb_handle *h) { return h ? h->m.err.c_str() : g_create_error.c_str(); }
 FB_API int fbo_run_signal(fb_handle *h, const fb_params *p, fb_signal_out *out) { ORACLE_TRY(h, run_signal(h->m, p, out)) }
