@@ -378,13 +378,16 @@ k_prox(Grid g, GflCtl *__restrict__ ctl, const double *__restrict__ beta, const 
     const double alpha = ctl->alpha;
     const double lam = ctl->lam / (alpha / 2.0);
     const int nchains = list ? nlist : g.nchains();   // sharded: the chains of this rank, longest first
-    if (side == 0 && lane == 0) ti[8] = atomicAdd(&ctl->next_chain, 1);
+    // the first chain of every team is assigned statically (team-major, so each SM gets a mix of lengths): no burst of
+    // ~1500 atomics on one address at kernel start; later chains come from the shared counter
+    const int nteams_all = gridDim.x * (blockDim.x >> 6);
+    if (side == 0 && lane == 0) ti[8] = team * gridDim.x + blockIdx.x;
     team_sync(bar);
     int qi = ti[8];
     while (qi < nchains) {
         const int q = list ? list[qi] : qi;
         int qnext = 0;
-        if (side == 0 && lane == 0) qnext = atomicAdd(&ctl->next_chain, 1); // published after this chain: latency hidden
+        if (side == 0 && lane == 0) qnext = nteams_all + atomicAdd(&ctl->next_chain, 1); // published after this chain: latency hidden
         long long t0 = 0, t1 = 0, t2 = 0;
         int nrounds = 0;
         if (trace) t0 = clock64();
