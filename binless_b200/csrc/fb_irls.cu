@@ -165,38 +165,29 @@ k_fin_expo(Tri t, int ntI, int ntJ, const double *__restrict__ part, double *__r
     if (threadIdx.x == 0) { items[2 * d] = a; items[2 * d + 1] = b; }
 }
 
+// one warp per bin: the row partials (by tile column) and column partials (by tile row) of every dataset, lane-strided
+// and then a butterfly sum: a fixed shape, so the result is the same on every run
 __global__ void __launch_bounds__(128)
 k_fin_bias(Tri t, int ntI, int ntJ, const double *__restrict__ part, double *__restrict__ items) {
-    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+    const int r = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
     const int n = t.n;
     if (r >= n) return;
-    const double *rowpart = part, *colpart = part + (int64_t)t.D * ntJ * n * 2;
+    const double2 *rp = reinterpret_cast<const double2 *>(part);
+    const double2 *cp = reinterpret_cast<const double2 *>(part + (int64_t)t.D * ntJ * n * 2);
     const int tj_min = ((r / TILE_I) * TILE_I) / TILE_J;
     int ti_max = ((r / TILE_J) * TILE_J + TILE_J - 1) / TILE_I;
     if (ti_max > ntI - 1) ti_max = ntI - 1;
-    // fixed summation order (dataset, then row partials by tile column, then column partials by tile row); the loads
-    // of eight terms are issued together so that the chain of additions, not the memory latency, sets the pace
+    const int nrow = ntJ - tj_min, ncol = ti_max + 1, per = nrow + ncol;
     double a = 0.0, b = 0.0;
-    const double2 *rp = reinterpret_cast<const double2 *>(rowpart), *cp = reinterpret_cast<const double2 *>(colpart);
-    for (int d = 0; d < t.D; ++d) {
-        for (int tJ = tj_min; tJ < ntJ; tJ += 8) {
-            double2 v[8];
-#pragma unroll
-            for (int q = 0; q < 8; ++q)
-                v[q] = (tJ + q < ntJ) ? __ldg(rp + ((int64_t)(d * ntJ + tJ + q) * n + r)) : make_double2(0.0, 0.0);
-#pragma unroll
-            for (int q = 0; q < 8; ++q) if (tJ + q < ntJ) { a += v[q].x; b += v[q].y; }
-        }
-        for (int tI = 0; tI <= ti_max; tI += 8) {
-            double2 v[8];
-#pragma unroll
-            for (int q = 0; q < 8; ++q)
-                v[q] = (tI + q <= ti_max) ? __ldg(cp + ((int64_t)(d * ntI + tI + q) * n + r)) : make_double2(0.0, 0.0);
-#pragma unroll
-            for (int q = 0; q < 8; ++q) if (tI + q <= ti_max) { a += v[q].x; b += v[q].y; }
-        }
+    for (int q = lane; q < t.D * per; q += 32) {
+        const int d = q / per, k = q - d * per;
+        const double2 v = k < nrow ? __ldg(rp + ((int64_t)(d * ntJ + tj_min + k) * n + r))
+                                   : __ldg(cp + ((int64_t)(d * ntI + (k - nrow)) * n + r));
+        a += v.x; b += v.y;
     }
-    items[2 * r] = a; items[2 * r + 1] = b;
+    a = warp_sum(a); b = warp_sum(b);
+    if (lane == 0) { items[2 * r] = a; items[2 * r + 1] = b; }
 }
 
 // one warp per diagonal
@@ -256,12 +247,19 @@ k_precision(Tri t, LegTables Lo, LegTables Ln, const double *__restrict__ phi_ol
             long long *__restrict__ keys) {
     const double INF = __longlong_as_double(0x7ff0000000000000LL);
     double dabs = -INF, mx = -INF, mn = INF;
-    EW_FOREACH_CELL(t) {
-        const int64_t idx = rowbase + off;
-        const double eo = log_expected(Lo, i, j, d, phi_old[idx]);
-        const double en = log_expected(Ln, i, j, d, phi_new[idx]);
-        dabs = fmax(dabs, fabs(en - eo));
-        mx = fmax(mx, en); mn = fmin(mn, en);
+    // a block walks rows blockIdx.y, blockIdx.y + gridDim.y, ... (a mix of long and short rows) and reduces once:
+    // one block per row spent most of its time in the reduction (28 800 blocks at 2400 bins x 4)
+    const int d = blockIdx.z, n = t.n;
+    for (int i = blockIdx.y; i < n; i += gridDim.y) {
+        const int64_t rowbase = (int64_t)d * t.ncells + rm_start(i, n);
+        for (int off = threadIdx.x; off < n - i; off += EW_THREADS) {
+            const int j = i + off;
+            const int64_t idx = rowbase + off;
+            const double eo = log_expected(Lo, i, j, d, phi_old[idx]);
+            const double en = log_expected(Ln, i, j, d, phi_new[idx]);
+            dabs = fmax(dabs, fabs(en - eo));
+            mx = fmax(mx, en); mn = fmin(mn, en);
+        }
     }
     __shared__ double s[3][EW_THREADS / 32];
     dabs = warp_max(dabs); mx = warp_max(mx); mn = warp_min(mn);
@@ -271,7 +269,11 @@ k_precision(Tri t, LegTables Lo, LegTables Ln, const double *__restrict__ phi_ol
     if (threadIdx.x == 0) {
         for (int k = 1; k < EW_THREADS / 32; ++k) { dabs = fmax(dabs, s[0][k]); mx = fmax(mx, s[1][k]); mn = fmin(mn, s[2][k]); }
         if (mx > -INF) {
-            atomicMax(&keys[0], dkey(dabs)); atomicMax(&keys[1], dkey(mx)); atomicMin(&keys[2], dkey(mn));
+            // ~29 000 blocks update three addresses: look first (a stale value only costs an unneeded atomic)
+            const long long ka = dkey(dabs), kx = dkey(mx), kn = dkey(mn);
+            if (ka > __ldcg(&keys[0])) atomicMax(&keys[0], ka);
+            if (kx > __ldcg(&keys[1])) atomicMax(&keys[1], kx);
+            if (kn < __ldcg(&keys[2])) atomicMin(&keys[2], kn);
         }
     }
 }
@@ -588,7 +590,7 @@ void leg_pass(int leg, int mode, const Tri &t, LegTables L, double alpha, const 
         k_fin_expo<<<t.D, 256, 0, st>>>(t, ntI, ntJ, part, items);
     } else if (leg == LEG_BIAS) {
         leg_pass_mode<LEG_BIAS>(mode, t, L, alpha, obs, nobs, phi, part, st);
-        k_fin_bias<<<(t.n + 127) / 128, 128, 0, st>>>(t, ntI, ntJ, part, items);
+        k_fin_bias<<<(t.n + 3) / 4, 128, 0, st>>>(t, ntI, ntJ, part, items);
     } else {
         leg_pass_mode<LEG_DECAY>(mode, t, L, alpha, obs, nobs, phi, part, st);
         k_fin_decay<<<(t.n + 3) / 4, 128, 0, st>>>(t, ntI, ntJ, part, items);
@@ -613,7 +615,7 @@ void precision(const Tri &t, LegTables Lold, LegTables Lnew, const double *phi_o
                double *scratch, double *out3, cudaStream_t st) {
     long long *keys = reinterpret_cast<long long *>(scratch);
     k_precision_init<<<1, 1, 0, st>>>(keys);
-    k_precision<<<ew_grid(t), EW_THREADS, 0, st>>>(t, Lold, Lnew, phi_old, phi_new, keys);
+    k_precision<<<dim3(1, (unsigned)std::min(t.n, 592), (unsigned)t.D), EW_THREADS, 0, st>>>(t, Lold, Lnew, phi_old, phi_new, keys);
     k_precision_fin<<<1, 1, 0, st>>>(keys, out3);
     FB_LAUNCH_CHECK();
 }
