@@ -332,9 +332,13 @@ __device__ __forceinline__ int taut_string_team(double *__restrict__ S, volatile
             status = 1; kend = kEnd;
             val = c + ((f.at(kEnd) - sg.s0) + aEnd) * recip<LONG>(R, rl, kEnd - sg.k0);
         }
-        if (lane == 0) { ti[side * 4] = status; ti[side * 4 + 1] = side ? L - kend : kend; ti[side * 4 + 2] = asign; }
+        // mailbox: one packed word per warp, double buffered by round parity, so ONE barrier per round is enough
+        // (the fills below touch only cells beyond the knots the other warp may still read)
+        const int slot = (nrounds & 1) * 2;
+        if (lane == 0) ti[slot + side] = ((side ? L - kend : kend) << 3) | ((asign + 1) << 1) | status;
         team_sync(bar);
-        const int ost = ti[(1 - side) * 4], oe = ti[(1 - side) * 4 + 1], oa = ti[(1 - side) * 4 + 2];
+        const int ow = ti[slot + 1 - side];
+        const int ost = ow & 1, oe = ow >> 3, oa = ((ow >> 1) & 3) - 1;
         int eL = dL, eR = dR;
         if (side ? ost : status) eL = side ? oe : kend;
         if (side ? status : ost) eR = side ? L - kend : oe;
@@ -352,8 +356,8 @@ __device__ __forceinline__ int taut_string_team(double *__restrict__ S, volatile
         }
         if (ost) { if (side) aL = oa; else aR = oa; }
         dL = eL; dR = eR;
-        team_sync(bar);
     }
+    team_sync(bar);      // every segment value is in S before either warp writes its half back
     return dL;
 }
 
@@ -934,7 +938,10 @@ int GflSolver::optimize(const double *d_y_tri, const double *d_w_tri, double lam
         done = true;
     }
     while (!done) {
-        for (int b = 0; b < POLL_BATCH; ++b) { iteration(y, w, parity); parity ^= 1; }
+        // sharded solves of large grids: an iteration (with its exchange) costs milliseconds, the poll microseconds,
+        // and iterations queued past convergence would still run their collectives
+        const int batch = (sharded_ && g_.ncells > 2000000) ? 1 : POLL_BATCH;
+        for (int b = 0; b < batch; ++b) { iteration(y, w, parity); parity ^= 1; }
         FB_LAUNCH_CHECK();
         FB_CUDA(cudaMemcpyAsync(h_ctl_, ctl_.p, sizeof(GflCtl), cudaMemcpyDeviceToHost, st_));
         FB_CUDA(cudaStreamSynchronize(st_));

@@ -324,3 +324,18 @@ def test_trail_block_sharding_on_two_gpus():
                         "--master-addr", "127.0.0.1", "--master-port", str(port),
                         os.path.join(ROOT, "tools", "shard_check.py")], capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and "SHARD CHECK PASS" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
+
+
+@pytest.mark.timeout(600)
+def test_gfl_global_scratch_default_size_matches_oracle(gpu_lib, oracle):
+    """4300 bins: fewer than six chains fit in shared memory, so the prox kernel keeps the prefix sums in global
+    scratch (15 teams per SM) by default. Eight ADMM iterations against the oracle (~10 s of CPU)."""
+    n = 4300; nc = n * (n + 1) // 2
+    rng = np.random.default_rng(43)
+    y = np.repeat(rng.normal(0, 1, nc // 30 + 1), 30)[:nc] + rng.normal(0, 0.5, nc)
+    w = rng.uniform(0, 3, nc)
+    a = gfl_solve(oracle, n, y, w, 2.5, 1e-12, 9, 0)
+    b = gfl_solve(gpu_lib, n, y, w, 2.5, 1e-12, 9, 0)
+    assert a["steps"] == b["steps"] == 9 and a["alpha"] == b["alpha"]
+    for k in ("beta", "z", "u"):
+        assert maxabs(a[k], b[k]) < ATOL, k
