@@ -940,7 +940,8 @@ int GflSolver::optimize(const double *d_y_tri, const double *d_w_tri, double lam
     while (!done) {
         // sharded solves of large grids: an iteration (with its exchange) costs milliseconds, the poll microseconds,
         // and iterations queued past convergence would still run their collectives
-        const int batch = (sharded_ && g_.ncells > 2000000) ? 1 : POLL_BATCH;
+        int batch = (sharded_ && g_.ncells > 2000000) ? 1 : POLL_BATCH;
+        if (const char *e = std::getenv("FB_SHARD_POLL")) batch = std::max(1, std::atoi(e));   // development aid
         for (int b = 0; b < batch; ++b) { iteration(y, w, parity); parity ^= 1; }
         FB_LAUNCH_CHECK();
         FB_CUDA(cudaMemcpyAsync(h_ctl_, ctl_.p, sizeof(GflCtl), cudaMemcpyDeviceToHost, st_));

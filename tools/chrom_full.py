@@ -19,10 +19,18 @@ ap.add_argument("--maxdiag", type=int, default=0)
 ap.add_argument("--seed", type=int, default=4)
 ap.add_argument("--rows-per-block", type=int, default=128)
 ap.add_argument("--nouter", type=int, default=25)
+ap.add_argument("--sharded", action="store_true", help="under torchrun: the ranks share every fused-lasso solve (trail blocks)")
 args = ap.parse_args()
 n, res = args.nbins, args.res
 nc = n * (n + 1) // 2
-dev = torch.device("cuda", 0)
+rank = int(os.environ.get("RANK", 0)); world = int(os.environ.get("WORLD_SIZE", 1)); local = int(os.environ.get("LOCAL_RANK", 0))
+torch.cuda.set_device(local)
+if args.sharded:
+    import torch.distributed as dist
+    from binless_b200.dist import init_comm
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+dev = torch.device("cuda", local)
+torch.manual_seed(args.seed); torch.cuda.manual_seed_all(args.seed)      # _standard_gamma draws from the default generator
 g = torch.Generator(device=dev); g.manual_seed(args.seed)
 t0 = time.time()
 cuts = torch.poisson(torch.full((n,), res / 256.0, device=dev), generator=g)
@@ -59,9 +67,19 @@ assert off == nc
 del bi, bj, d, nobs, ld, eta, mean, size, lam, obs, m
 torch.cuda.empty_cache()
 t_gen = time.time() - t0
-print(f"generated {nc} cells in {t_gen:.1f} s, {cols['observed'].sum()} reads", flush=True)
+if rank == 0:
+    print(f"generated {nc} cells in {t_gen:.1f} s, {cols['observed'].sum()} reads", flush=True)
 mat = dict(cols, name=None, bin1=None, bin2=None)
 lib = cuda_lib()
+import zlib
+in_crc = zlib.crc32(cols["observed"].tobytes()) ^ zlib.crc32(cols["nobs"].tobytes())
+if args.sharded:
+    t_in = torch.tensor([in_crc], dtype=torch.int64, device=dev)
+    lo = t_in.clone(); dist.all_reduce(lo, op=dist.ReduceOp.MIN); hi = t_in.clone(); dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+    if lo.item() != hi.item():
+        raise SystemExit("the ranks generated different inputs: the sharded solve needs identical calls on every rank")
+    init_comm(lib)      # every rank generated the same matrix (same seed, same GPU model) and makes the same calls
+    dist.barrier()
 t0 = time.time()
 h = lib.create(mat, n)
 t_create = time.time() - t0
@@ -74,10 +92,19 @@ ls = out["log_signal"]
 ok = bool(np.isfinite(ls).all() and ls.min() == 0.0 and np.isfinite(out["biases"]["estimate"]).all()
           and np.all(np.diff(out["decay"]["beta"][30:]) <= 1e-9))
 h.close()
-print(json.dumps({"workload": f"fast_binless, {n} bins x 1 dataset ({nc} cells), res {res}, maxdiag {args.maxdiag}, lam2 2.5",
+if args.sharded:
+    import zlib
+    sig = torch.tensor([zlib.crc32(ls.tobytes())], dtype=torch.int64, device=dev)
+    lo = sig.clone(); dist.all_reduce(lo, op=dist.ReduceOp.MIN); hi = sig.clone(); dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+    ok = ok and bool(lo.item() == hi.item())      # every rank holds the same log_signal, bit for bit
+if rank == 0:
+  print(json.dumps({"workload": f"fast_binless, {n} bins x 1 dataset ({nc} cells), res {res}, maxdiag {args.maxdiag}, lam2 2.5",
                   "properties_ok": ok, "outer_steps": int(dg["nsteps"]), "converged": bool(dg["converged"]),
                   "admm_iters_per_solve": [int(x) for x in dg["solve_iters"]], "seconds_create": t_create,
                   "seconds_run": t_run, "ms_device": dg["ms_total"], "ms_solver": dg["ms_solver"],
                   "Mcell_iter_per_s": dg["admm_cell_iters"] / t_run / 1e6,
-                  "log_signal_max": float(ls.max()), "frac_signal_nonzero": float((ls > 0).mean())}), flush=True)
+                  "log_signal_max": float(ls.max()), "frac_signal_nonzero": float((ls > 0).mean()),
+                  "n_gpus": world if args.sharded else 1, "input_crc32": in_crc, "log_signal_crc32": __import__("zlib").crc32(ls.tobytes())}), flush=True)
+if args.sharded:
+    dist.destroy_process_group()
 sys.exit(0 if ok else 1)
