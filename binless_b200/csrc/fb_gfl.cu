@@ -4,16 +4,17 @@
 //   k_beta  closed-form beta update over 32x32 tiles of the triangle, reading the row duals in
 //           row-major and the column duals in column-major order (shared-memory tile transpose);
 //           writes beta twice: row-major (input of the row chains) and column-major (column chains)
-//   k_prox  persistent kernel, one WARP per chain (dynamic longest-first queue): stages the prefix sums
-//           of beta+u of one chain in shared memory, runs the exact 1-D fused-lasso prox as a
-//           warp-cooperative taut string (same unique minimiser as tf_dp_weight, gfl_tf.c:184-321:
-//           32 candidate end points per round, slope bounds by warp scans, first tube violation by
-//           ballot), then streams z, u += beta - z (gfl_graph_fl.c:306-327) and the residual sums
+//   k_prox  persistent kernel, two WARPS per chain working from both ends in lock step (static first chain, then a
+//           dynamic longest-first queue): stages the prefix sums of beta+u of one chain in shared memory (or, for
+//           chains too long for ten of them to fit, in a per-team slot of global scratch), runs the exact 1-D
+//           fused-lasso prox as a warp-cooperative taut string (same unique minimiser as tf_dp_weight,
+//           gfl_tf.c:184-321: 160 candidate end points per round, slope bounds by warp scans, first tube violation
+//           by ballot), then streams z, u += beta - z (gfl_graph_fl.c:306-327) and the residual sums
 //           (gfl_graph_fl.c:329-365) with coalesced accesses
 //   k_ctl   single block: fixed-order reduction of the per-chain partials, convergence test,
 //           varying-penalty rule every 50 steps (gfl_graph_fl.c:163-181)
-// The host polls the control block every few iterations; once `done` is set the remaining queued
-// launches return immediately.
+// The loop itself is ONE graph launch (WHILE conditional node, condition set by k_ctl); with collectives between
+// the kernels (trail-block sharding over NCCL, fb_comm.cuh) or FB_NO_GRAPH the host polls the control block instead.
 #include "fb_gfl.cuh"
 #include "fb_comm.cuh"
 #include <algorithm>
@@ -189,7 +190,7 @@ struct Seg {
 // are not on the critical path are not unrolled: the team kernel is instruction-cache bound otherwise.
 constexpr int B = PBR;
 // 1/m: from the shared-memory table when m < rl, else the same correctly rounded quotient computed in place
-// (LONG chains: the table covers the first rl distances only so that the prefix sums of a 27 000-cell chain fit)
+// (LONG: beyond ~28 000 cells the table no longer fits in shared memory and covers the first rl distances only)
 template <bool LONG>
 __device__ __forceinline__ double recip(const double *__restrict__ R, const int rl, const int m) {
     if (LONG) return m < rl ? R[m] : 1.0 / (double)m;

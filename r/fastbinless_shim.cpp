@@ -140,3 +140,35 @@ DataFrame fast_binless_difference_cuda(const List out, int ref, double alpha, co
 //   function("fast_binless_difference", &fast_binless_difference_cuda, List::create(_["out"], _["ref"], _["alpha"],
 //            _["lam2"], _["lam1"]=0., _["tol_val"]=2e-1, _["compute_patchnos"]=true, _["maxdiag"]=0),
 //            "documentation for fast_binless_difference ");
+
+// ---- input side: bin_data(cs, resolution) for a CSnorm object (R/preprocess.R:114-146) on the device -----------------
+// biases = cs@biases[, .(name, pos)] and counts = cs@counts[, .(name, pos1, pos2, contact.close, contact.far, contact.up,
+// contact.down)] with `name` as integer codes; returns the data.table columns bin_data() builds (begin/end follow from
+// pos and resolution in R).
+// [[Rcpp::export]]
+DataFrame bin_data_cuda(const DataFrame biases, const DataFrame counts, int ndatasets, int resolution) {
+    IntegerVector cn = biases["name"], cp = biases["pos"];
+    IntegerVector rn = counts["name"], p1 = counts["pos1"], p2 = counts["pos2"];
+    IntegerVector cc = counts["contact.close"], cf = counts["contact.far"], cu = counts["contact.up"], cd = counts["contact.down"];
+    fb_reads r;
+    r.ndatasets = ndatasets; r.resolution = resolution;
+    r.ncuts = cn.size(); r.cut_name = cn.begin(); r.cut_pos = cp.begin();
+    r.nreads = rn.size(); r.rd_name = rn.begin(); r.rd_pos1 = p1.begin(); r.rd_pos2 = p2.begin();
+    r.contact_close = cc.begin(); r.contact_far = cf.begin(); r.contact_up = cu.begin(); r.contact_down = cd.begin();
+    HandleGuard g;
+    int nbins = 0;
+    check(fb_create_binned(&r, &nbins, &g.h), NULL);
+    const R_xlen_t N = fb_mat_rows(g.h);
+    IntegerVector name(N), bin1(N), pos1(N), bin2(N), pos2(N), observed(N), nobs(N);
+    NumericVector distance(N);
+    check(fb_get_mat(g.h, name.begin(), bin1.begin(), pos1.begin(), bin2.begin(), pos2.begin(), distance.begin(),
+                     observed.begin(), nobs.begin()), g.h);
+    return DataFrame::create(_["name"] = name, _["bin1"] = bin1, _["pos1"] = pos1, _["bin2"] = bin2, _["pos2"] = pos2,
+                             _["distance"] = distance, _["observed"] = observed, _["nobs"] = nobs);
+}
+
+// ---- multi-GPU: one R process per GPU (e.g. under mpirun); the 128-byte id travels by whatever the host has --------
+// [[Rcpp::export]]
+RawVector fastbinless_comm_id() { RawVector id(128); check(fb_comm_unique_id(id.begin()), NULL); return id; }
+// [[Rcpp::export]]
+void fastbinless_comm_init(int rank, int world, RawVector id) { check(fb_comm_init(rank, world, world > 1 ? id.begin() : NULL), NULL); }

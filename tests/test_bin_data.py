@@ -45,6 +45,32 @@ def test_hand_checked_edges(oracle_port):
         assert m["distance"].tolist() == [5.0, 15.0, 25.0, 5.0, 15.0, 5.0]
 
 
+def check_bin_golden(lib, name):
+    import os, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    sys.path.insert(0, os.path.join(root, "tools"))
+    from make_golden import BIN_CASES
+    c = BIN_CASES[name]
+    g = np.load(os.path.join(root, "tests", "golden", name + ".npz"))
+    r = synth_reads(c["n"], c["D"], c["res"], c["seed"])
+    assert sum(int(r[k].astype(np.int64).sum()) for k in r) == int(g["reads_sum"]), "synthetic read generator drifted"
+    with lib.create_binned(r, c["res"], c["D"]) as h:
+        assert h.nbins == int(g["nbins"])
+        for k in ("observed", "nobs", "pos1", "pos2", "distance"):
+            assert np.array_equal(h.cols[k], g[k]), k
+
+
+@pytest.mark.parametrize("name", ["bin_data_n33_d2", "bin_data_n64_d2_res777"])
+def test_oracle_binning_reproduces_golden(oracle_port, name):
+    check_bin_golden(oracle_port, name)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["bin_data_n33_d2", "bin_data_n64_d2_res777"])
+def test_device_binning_reproduces_golden(gpu_lib, name):
+    check_bin_golden(gpu_lib, name)
+
+
 def test_errors(oracle_port):
     from binless_b200._abi import FastBinlessError
     r = synth_reads(5, 1, 1000, 1)

@@ -9,7 +9,7 @@ import pytest
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, os.path.join(ROOT, "tools"))
-from make_golden import CASES  # noqa: E402
+from make_golden import BIN_CASES, CASES  # noqa: E402
 from binless_b200.synth import synth  # noqa: E402
 
 
@@ -49,4 +49,4 @@ def test_oracle_reproduces_golden(oracle_port, name):
 
 def test_golden_files_present():
     files = {os.path.basename(f)[:-4] for f in glob.glob(os.path.join(ROOT, "tests", "golden", "*.npz"))}
-    assert files == set(CASES)
+    assert files == set(CASES) | set(BIN_CASES)

@@ -18,7 +18,23 @@ CASES = {
     "n120_d1_tight": dict(n=120, D=1, seed=9, alpha=0.5, lam2=[2.5], lam1=[0.05], kw=dict(tol_val=0.01, nouter=6, bg_steps=2)),
 }
 
+# input side (bin_data): the numpy statement-by-statement restatement of R/preprocess.R:114-146 on seeded reads
+BIN_CASES = {"bin_data_n33_d2": dict(n=33, D=2, res=2000, seed=2), "bin_data_n64_d2_res777": dict(n=64, D=2, res=777, seed=4)}
+
+
+def make_bin_golden(outdir):
+    from binless_b200.synth import bin_reads_numpy, synth_reads
+    for name, c in BIN_CASES.items():
+        r = synth_reads(c["n"], c["D"], c["res"], c["seed"])
+        m = bin_reads_numpy(r, c["res"], c["D"])
+        np.savez_compressed(os.path.join(outdir, name + ".npz"), observed=m["observed"], nobs=m["nobs"], pos1=m["pos1"],
+                            pos2=m["pos2"], distance=m["distance"], nbins=np.int64(m["nbins"]),
+                            reads_sum=np.int64(sum(int(r[k].astype(np.int64).sum()) for k in r)))
+        print(name, "bins", m["nbins"], "reads", int(m["observed"].sum()))
+
+
 def main():
+    make_bin_golden(os.path.join(ROOT, "tests", "golden"))
     ora = oracle_lib("reference")
     outdir = os.path.join(ROOT, "tests", "golden")
     os.makedirs(outdir, exist_ok=True)
