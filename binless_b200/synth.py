@@ -13,7 +13,7 @@ from __future__ import annotations
 
 import numpy as np
 
-__all__ = ["synth", "synth_reads", "bin_reads_numpy", "tri_indices", "CONFIGS"]
+__all__ = ["synth", "synth_reads", "tri_indices", "CONFIGS"]
 
 # the named workloads of BASELINE.json / SURVEY.md section 8
 CONFIGS = {
@@ -138,44 +138,3 @@ def synth_reads(nbins: int, ndatasets: int, res: int = 5000, seed: int = 1, read
     out = {"cut_name": np.concatenate(cut_name).astype(np.int32), "cut_pos": np.concatenate(cut_pos).astype(np.int32)}
     out.update({k: np.concatenate(v).astype(np.int32) for k, v in rd.items()})
     return out
-
-
-def bin_reads_numpy(reads, res: int, ndatasets: int):
-    """TEST INFRASTRUCTURE: bin_data() for a CSnorm object restated with numpy, statement by statement
-    (R/preprocess.R:114-146, add_bin_bounds_and_distance R/common.R:115-132). Returns the ``mat`` columns."""
-    pos = reads["cut_pos"].astype(np.int64)
-    borders = np.arange(pos.min() - 1, pos.max() + 1 + 1, res)         # seq(min(pos)-1, max(pos)+1, resolution)
-    nb = borders.size - 1                                               # the last incomplete bin is discarded
-    def cut(p):                                                         # cut(.., right=F, include.lowest=T); -1 = NA
-        p = np.asarray(p, dtype=np.int64)
-        b = np.searchsorted(borders, p, side="right") - 1
-        b[p == borders[-1]] = nb - 1
-        b[(p < borders[0]) | (p > borders[-1])] = -1
-        return b
-    bi, bj = tri_indices(nb)
-    nc = bi.size
-    cols = {k: [] for k in ("name", "bin1", "pos1", "bin2", "pos2", "distance", "observed", "nobs")}
-    for d in range(ndatasets):
-        sel = reads["cut_name"] == d + 1
-        b = cut(pos[sel]); b = b[b >= 0]
-        ncut = np.bincount(b, minlength=nb).astype(np.int64)
-        nobs = 4 * ncut[bi] * ncut[bj]
-        nobs[bi == bj] //= 2                                            # as.integer(nobs / 2)
-        rs = reads["rd_name"] == d + 1
-        b1 = cut(reads["rd_pos1"][rs]); b2 = cut(reads["rd_pos2"][rs])
-        tot = (reads["contact_close"][rs].astype(np.int64) + reads["contact_far"][rs] + reads["contact_up"][rs] + reads["contact_down"][rs])
-        ok = (b1 >= 0) & (b2 >= 0) & (b1 <= b2)
-        cell = b1[ok] * nb - b1[ok] * (b1[ok] - 1) // 2 + (b2[ok] - b1[ok])
-        observed = np.bincount(cell, weights=tot[ok], minlength=nc).astype(np.int64)
-        present = np.bincount(cell, minlength=nc) > 0                   # rows of poscounts; absent -> is.na(observed)
-        nobs[~present] = 0; observed[~present] = 0
-        observed[nb - 1] += 1
-        begin = borders[:-1]; end = borders[1:]
-        p = ((end + begin) // 2).astype(np.int32)                       # as.integer((end + begin) / 2)
-        cols["name"].append(np.full(nc, d + 1, dtype=np.int32)); cols["bin1"].append(bi + 1); cols["bin2"].append(bj + 1)
-        cols["pos1"].append(p[bi]); cols["pos2"].append(p[bj])
-        cols["distance"].append((begin[bj] - begin[bi]) + res / 2.0)
-        cols["observed"].append(observed.astype(np.int32)); cols["nobs"].append(nobs.astype(np.int32))
-    mat = {k: np.ascontiguousarray(np.concatenate(v)) for k, v in cols.items()}
-    mat["nbins"] = int(nb)
-    return mat

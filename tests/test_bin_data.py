@@ -1,14 +1,20 @@
 """bin_data() on the input side (/root/reference/binless/R/preprocess.R:114-146, R/common.R:115-132).
 
 CPU: the oracle's loop restatement (fbo_create_binned) against the statement-by-statement numpy restatement
-(binless_b200.synth.bin_reads_numpy) -- integer work, bit-exact -- and hand-checked edge cases. The reference's R code
+(oracle/bin_data_numpy.py) -- integer work, bit-exact -- and hand-checked edge cases. The reference's R code
 cannot run here (no R), so this row is "parity unpinned" by the reference itself, like the driver rows.
 GPU (-m gpu): fb_create_binned builds the same matrix on the device, bit for bit, and fast_binless on that handle equals
 fast_binless on the host-binned matrix."""
+import os
+import sys
+
 import numpy as np
 import pytest
 
-from binless_b200.synth import bin_reads_numpy, synth_reads
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle"))
+from bin_data_numpy import bin_reads_numpy  # noqa: E402
+
+from binless_b200.synth import synth_reads
 
 COLS = ("name", "bin1", "pos1", "bin2", "pos2", "observed", "nobs", "distance")
 CASES = [(7, 1, 5000, 1), (33, 2, 2000, 2), (100, 3, 5000, 3), (64, 2, 777, 4), (1, 1, 5000, 5), (2, 2, 101, 6)]

@@ -4,7 +4,9 @@ import json, sys, time
 import numpy as np
 sys.path.insert(0, '.')
 from binless_b200 import cuda_lib
-from binless_b200.synth import bin_reads_numpy, synth_reads
+sys.path.insert(0, 'oracle')
+from bin_data_numpy import bin_reads_numpy
+from binless_b200.synth import synth_reads
 n, D, res = 2400, 4, 5000
 nreads = int(sys.argv[1]) if len(sys.argv) > 1 else 5_000_000
 r = synth_reads(n, D, res, 2, reads_per_dataset=nreads)

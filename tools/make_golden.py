@@ -23,7 +23,9 @@ BIN_CASES = {"bin_data_n33_d2": dict(n=33, D=2, res=2000, seed=2), "bin_data_n64
 
 
 def make_bin_golden(outdir):
-    from binless_b200.synth import bin_reads_numpy, synth_reads
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    from bin_data_numpy import bin_reads_numpy
+    from binless_b200.synth import synth_reads
     for name, c in BIN_CASES.items():
         r = synth_reads(c["n"], c["D"], c["res"], c["seed"])
         m = bin_reads_numpy(r, c["res"], c["D"])
