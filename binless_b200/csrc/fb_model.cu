@@ -211,8 +211,8 @@ void Model::ingest(int nbins, const fb_mat *m) {
             return nullptr;
         });
     });
-    FB_CUDA(cudaMemcpyAsync(obs_.p, m->observed, N * sizeof(int32_t), cudaMemcpyHostToDevice, st_));
-    FB_CUDA(cudaMemcpyAsync(nobs_.p, m->nobs, N * sizeof(int32_t), cudaMemcpyHostToDevice, st_));
+    upload_bytes(obs_.p, m->observed, N * sizeof(int32_t));
+    upload_bytes(nobs_.p, m->nobs, N * sizeof(int32_t));
     { // same buffers as alloc_work(), without its synchronisation: the validation below overlaps the uploads
         phi_.alloc(N); phi_new_.alloc(N); phihat_.alloc(N); wgt_.alloc(N);
         phi_.zero(st_); phihat_.zero(st_); wgt_.zero(st_);
@@ -395,6 +395,43 @@ void Model::download_bytes(void *h_dst, const void *d_src, size_t bytes) {
         });
     }
     for (int b = 0; b < NB; ++b) { if (busy[b].valid()) busy[b].get(); cudaEventDestroy(ev[b]); BlockCache::host().put(stage[b], CHUNK); }
+}
+
+// Host -> device, the mirror image: large pageable sources are copied into pinned staging by several host threads
+// and sent chunk by chunk, so the DMA of one chunk overlaps the host copy of the next.
+void Model::upload_bytes(void *d_dst, const void *h_src, size_t bytes) {
+    if (!bytes) return;
+    constexpr size_t CHUNK = size_t(32) << 20;
+    cudaPointerAttributes at{};
+    const bool known = cudaPointerGetAttributes(&at, h_src) == cudaSuccess;
+    if (!known) cudaGetLastError();
+    const bool pageable = !known || at.type == cudaMemoryTypeUnregistered;
+    if (!pageable || bytes < 2 * CHUNK) {
+        FB_CUDA(cudaMemcpyAsync(d_dst, h_src, bytes, cudaMemcpyHostToDevice, st_));
+        return;
+    }
+    constexpr int NB = 3;
+    void *stage[NB]; cudaEvent_t ev[NB]; bool used[NB] = {false, false, false};
+    for (int b = 0; b < NB; ++b) { stage[b] = BlockCache::host().get(CHUNK); FB_CUDA(cudaEventCreateWithFlags(&ev[b], cudaEventDisableTiming)); }
+    const int nthr = std::max(1, std::min(8, host_threads()));
+    size_t off = 0;
+    for (int i = 0; off < bytes; ++i, off += CHUNK) {
+        const int b = i % NB;
+        const size_t len = std::min(CHUNK, bytes - off);
+        if (used[b]) FB_CUDA(cudaEventSynchronize(ev[b]));       // the DMA out of this staging buffer has finished
+        char *dst = static_cast<char *>(stage[b]); const char *src = static_cast<const char *>(h_src) + off;
+        std::vector<std::thread> th;
+        const size_t part = (len + nthr - 1) / nthr;
+        for (int t = 1; t < nthr; ++t)
+            if ((size_t)t * part < len) th.emplace_back([=] { std::memcpy(dst + t * part, src + t * part, std::min(part, len - t * part)); });
+        std::memcpy(dst, src, std::min(part, len));
+        for (auto &x : th) x.join();
+        FB_CUDA(cudaMemcpyAsync(static_cast<char *>(d_dst) + off, stage[b], len, cudaMemcpyHostToDevice, st_));
+        FB_CUDA(cudaEventRecord(ev[b], st_));
+        used[b] = true;
+    }
+    FB_CUDA(cudaStreamSynchronize(st_));
+    for (int b = 0; b < NB; ++b) { cudaEventDestroy(ev[b]); BlockCache::host().put(stage[b], CHUNK); }
 }
 
 void Model::download(double *h_dst, const double *d_src, size_t cnt) { download_bytes(h_dst, d_src, cnt * sizeof(double)); }

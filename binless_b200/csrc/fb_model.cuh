@@ -91,6 +91,7 @@ private:
     void patchnos(const double *d_value, double tol, bool compute, int32_t *h_out);
     void download(double *h_dst, const double *d_src, size_t n);
     void download_bytes(void *h_dst, const void *d_src, size_t bytes);
+    void upload_bytes(void *d_dst, const void *h_src, size_t bytes);
 };
 
 extern std::string g_last_error;
