@@ -32,8 +32,8 @@ constexpr int CTL_THREADS = 1024;
 constexpr int POLL_BATCH = 8;
 constexpr int PROX_MAX_TEAMS = 10;    // two warps per chain; 640 threads leave 96 registers per thread (instruction bound:
                                       // more teams with fewer registers are slower at 2400 bins, 261 -> 299 us with 12)
-constexpr int PROX_GS_TEAMS = 15;     // chains in global scratch are latency bound: 15 teams (64 registers, named barriers
-                                      // 1..15) are faster there (12 000 bins: 17.4 -> 13.3 ms per iteration)
+constexpr int PROX_GS_TEAMS = 15;     // chains in global scratch pay L1/L2 latency in every round: 15 teams (64 registers,
+                                      // named barriers 1..15) are faster there (12 000 bins: 17.4 -> 13.3 ms per iteration)
 constexpr unsigned FULL = 0xffffffffu;
 
 // --------------------------------------------------------------------------
