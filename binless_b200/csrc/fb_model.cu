@@ -86,6 +86,16 @@ void write_signal_csv(const char *path, int64_t N, const double *const cols[7]) 
     std::fclose(f);
 }
 
+// copies of at least this many bytes to / from pageable host memory are pipelined through pinned staging
+// (FB_STAGE_MIN_MB lowers the limit so that the tests exercise the path at small sizes)
+size_t stage_min_bytes() {
+    static const size_t v = [] {
+        const char *e = std::getenv("FB_STAGE_MIN_MB");
+        return e ? (size_t)std::max(1, std::atoi(e)) << 20 : size_t(64) << 20;
+    }();
+    return v;
+}
+
 int host_threads() {
     unsigned h = std::thread::hardware_concurrency();
     return (int)std::min(16u, std::max(1u, h));
@@ -368,7 +378,7 @@ void Model::download_bytes(void *h_dst, const void *d_src, size_t bytes) {
     const bool known = cudaPointerGetAttributes(&at, h_dst) == cudaSuccess;
     if (!known) cudaGetLastError();
     const bool pageable = !known || at.type == cudaMemoryTypeUnregistered;
-    if (!pageable || bytes < 2 * CHUNK) {
+    if (!pageable || bytes < stage_min_bytes()) {
         FB_CUDA(cudaMemcpyAsync(h_dst, d_src, bytes, cudaMemcpyDeviceToHost, st_));
         return;
     }
@@ -406,7 +416,7 @@ void Model::upload_bytes(void *d_dst, const void *h_src, size_t bytes) {
     const bool known = cudaPointerGetAttributes(&at, h_src) == cudaSuccess;
     if (!known) cudaGetLastError();
     const bool pageable = !known || at.type == cudaMemoryTypeUnregistered;
-    if (!pageable || bytes < 2 * CHUNK) {
+    if (!pageable || bytes < stage_min_bytes()) {
         FB_CUDA(cudaMemcpyAsync(d_dst, h_src, bytes, cudaMemcpyHostToDevice, st_));
         return;
     }

@@ -339,3 +339,26 @@ def test_gfl_global_scratch_default_size_matches_oracle(gpu_lib, oracle):
     assert a["steps"] == b["steps"] == 9 and a["alpha"] == b["alpha"]
     for k in ("beta", "z", "u"):
         assert maxabs(a[k], b[k]) < ATOL, k
+
+
+def test_pipelined_pageable_copies_change_nothing(oracle):
+    """Large copies to / from pageable host memory go through pinned staging in 32 MB chunks (fb_model.cu:
+    upload_bytes / download_bytes). FB_STAGE_MIN_MB=1 (read once per process, hence the subprocess) forces that path
+    at a small size; inputs, outputs and labels must equal the direct path bit for bit."""
+    import subprocess
+    code = (
+        "import sys, zlib, numpy as np; sys.path.insert(0, %r)\n"
+        "from binless_b200 import cuda_lib\n"
+        "from binless_b200.synth import synth\n"
+        "mat = synth(700, 3, 5000, 5)\n"
+        "with cuda_lib().create(mat, 700) as h:\n"
+        "    o = h.run_signal(0.5, 2.5, 0.05)\n"
+        "print(' '.join(str(zlib.crc32(np.ascontiguousarray(o[k]).tobytes())) for k in\n"
+        "      ('log_signal', 'phihat', 'weight', 'signal', 'binless', 'background', 'patchno')))\n" % ROOT)
+    outs = []
+    for env_extra in ({}, {"FB_STAGE_MIN_MB": "1"}):
+        env = dict(os.environ); env.pop("FB_STAGE_MIN_MB", None); env.update(env_extra)
+        r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=env, timeout=300)
+        assert r.returncode == 0, r.stderr[-2000:]
+        outs.append(r.stdout.strip().splitlines()[-1])
+    assert outs[0] == outs[1]
