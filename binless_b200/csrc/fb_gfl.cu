@@ -113,16 +113,6 @@ k_beta(Grid g, const GflCtl *__restrict__ ctl, const double *__restrict__ y, con
 // drops below the running maximum of lo. 32 candidates k are examined per round: running bounds by warp
 // scans, first violation by ballot. Finished segments overwrite S in place with their value c + slope.
 // --------------------------------------------------------------------------
-__device__ __forceinline__ double scan_min_incl(double v, int lane) {
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) { const double t = __shfl_up_sync(FULL, v, o); if (lane >= o) v = fmin(v, t); }
-    return v;
-}
-__device__ __forceinline__ double scan_max_incl(double v, int lane) {
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) { const double t = __shfl_up_sync(FULL, v, o); if (lane >= o) v = fmax(v, t); }
-    return v;
-}
 __device__ __forceinline__ double scan_sum_incl(double v, int lane) {
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) { const double t = __shfl_up_sync(FULL, v, o); if (lane >= o) v += t; }
