@@ -9,6 +9,9 @@ Workload (config.workload): BASELINE.json configs[1] -- synthetic chr7 12 Mb loc
 fast_binless call on that batch. With N > 1 every rank runs its own locus of the same shape (independent units,
 no data-path collective; weak scaling) and `value` is the sum over ranks divided by the slowest rank's time.
 
+Timing: whole calls between barrier + cudaDeviceSynchronize pairs (max over ranks); `device_ms_per_step` is the same
+call measured with CUDA events on the library's own stream (rank 0), which torch.cuda.Event cannot see.
+
 metric = M cell*iter/s: ADMM cell-iterations of the whole call (sum over fused-lasso solves of cells x iterations,
 identical to the oracle's counts) divided by the time of the whole call.
   value : inputs resident in HBM, results left in HBM (fb_run_signal on an existing handle)
@@ -208,7 +211,7 @@ def run_cuda(args):
     achieved = ADMM_BYTES_PER_CELL_ITER * ncells / sec_per_iter / 1e9
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": t_value / args.steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "ms_per_step": t_value / args.steps * 1e3, "device_ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic",
         "config": {"workload": WORKLOAD, "nbins": n, "ndatasets": D, "cells_per_dataset": ncells,
                    "outer_steps": int(nsteps_outer), "admm_iters_per_solve": solve_iters,
