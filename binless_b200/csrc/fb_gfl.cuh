@@ -8,9 +8,12 @@
 // (paths relative to /root/reference/binless/src). See DESIGN.md for the layout.
 #pragma once
 #include "fb_util.cuh"
+#include <memory>
 #include <vector>
 
 namespace fb {
+
+struct LanePlan;   // fb_prox_lane.cuh
 
 // Geometry of the solved grid: upper-triangular band of width md (md == n is the
 // full triangle). Cells (i,j), 0 <= j-i < md.
@@ -136,6 +139,10 @@ private:
     bool prox_long_ = false;           // reciprocal table shorter than the longest chain
     bool prox_gs_ = false;             // prefix sums of the chains in global scratch instead of shared memory
     DevBuf<double> gscratch_;
+    // split-and-verify chain prox (fb_prox_lane.cu): used whenever the longest chain fits one CTA's shared memory;
+    // FB_PROX_LANE=0 keeps the team kernel k_prox (A/B tests)
+    std::unique_ptr<LanePlan> lane_;
+    bool use_lane_ = false;
     cudaEvent_t ev0_, ev1_;
     // the whole ADMM loop as ONE graph launch: a WHILE conditional node whose body is one iteration, the condition
     // set on the device by k_ctl (no host polling, no launches queued past convergence)
