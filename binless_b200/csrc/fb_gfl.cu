@@ -18,7 +18,7 @@
 #include "fb_gfl.cuh"
 #include "fb_comm.cuh"
 #include "fb_taut.cuh"
-#include "fb_prox_lane.cuh"
+#include "fb_prox_aset.cuh"
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
@@ -537,11 +537,11 @@ GflSolver::GflSolver(int nbins, unsigned maxdiag, cudaStream_t stream) : nbins_(
     FB_CUDA(cudaEventCreate(&ev0_)); FB_CUDA(cudaEventCreate(&ev1_));
     r0_ = c0_ = 0; r1_ = c1_ = g_.n;
     if (Comm::get().active()) setup_shard();
-    lane_.reset(new LanePlan());
+    aset_.reset(new AsetPlan());
     {
-        const char *e = std::getenv("FB_PROX_LANE");
-        if (!(e && std::atoi(e) == 0) && !trace_.p) lane_plan_build(*lane_, g_, r0_, r1_, c0_, c1_, n_sm_);
-        use_lane_ = lane_->usable;
+        const char *e = std::getenv("FB_PROX_ASET");
+        if (!(e && std::atoi(e) == 0) && !trace_.p) aset_plan_build(*aset_, g_, r0_, r1_, c0_, c1_, n_sm_);
+        use_aset_ = aset_->usable;
     }
     // the polling loop stays for the sharded solve (collectives between the kernels) and the trace aid
     use_graph_ = !sharded_ && !trace_.p && st_ != nullptr && !std::getenv("FB_NO_GRAPH");
@@ -697,7 +697,7 @@ void GflSolver::launch_iteration(const double *y, const double *w, bool in_graph
     k_beta<<<tg, tb, 0, st_>>>(g_, ctl_.p, y, w, zr_.p, ur_.p, zc_.p, uc_.p, beta_.p, betaT_.p, r0_, r1_, c0_, c1_);
     tmark(1);
     const int *list = sharded_ ? chain_list_.p : nullptr;
-    if (use_lane_) lane_prox_launch(*lane_, ctl_.p, beta_.p, betaT_.p, zr_.p, ur_.p, zc_.p, uc_.p, partials_.p, st_);
+    if (use_aset_) aset_prox_launch(*aset_, ctl_.p, beta_.p, betaT_.p, zr_.p, ur_.p, zc_.p, uc_.p, partials_.p, st_);
     else
 #define FB_PROX_LAUNCH(LONG_, GS_)                                                                                              \
     k_prox<LONG_, GS_><<<prox_grid_, 64 * prox_warps_, prox_smem_, st_>>>(g_, ctl_.p, beta_.p, betaT_.p, zr_.p, ur_.p, zc_.p, uc_.p,  \

@@ -13,7 +13,7 @@
 
 namespace fb {
 
-struct LanePlan;   // fb_prox_lane.cuh
+struct AsetPlan;   // fb_prox_aset.cuh
 
 // Geometry of the solved grid: upper-triangular band of width md (md == n is the
 // full triangle). Cells (i,j), 0 <= j-i < md.
@@ -139,10 +139,10 @@ private:
     bool prox_long_ = false;           // reciprocal table shorter than the longest chain
     bool prox_gs_ = false;             // prefix sums of the chains in global scratch instead of shared memory
     DevBuf<double> gscratch_;
-    // split-and-verify chain prox (fb_prox_lane.cu): used whenever the longest chain fits one CTA's shared memory;
-    // FB_PROX_LANE=0 keeps the team kernel k_prox (A/B tests)
-    std::unique_ptr<LanePlan> lane_;
-    bool use_lane_ = false;
+    // parallel active-set chain prox (fb_prox_aset.cu): used whenever the longest chain fits one CTA's shared memory;
+    // FB_PROX_ASET=0 keeps the taut-string team kernel k_prox (A/B tests)
+    std::unique_ptr<AsetPlan> aset_;
+    bool use_aset_ = false;
     cudaEvent_t ev0_, ev1_;
     // the whole ADMM loop as ONE graph launch: a WHILE conditional node whose body is one iteration, the condition
     // set on the device by k_ctl (no host polling, no launches queued past convergence)

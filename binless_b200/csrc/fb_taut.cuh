@@ -1,5 +1,5 @@
-// fb_taut.cuh -- warp-cooperative taut-string search shared by the chain-prox kernels (fb_gfl.cu: two warps per
-// chain from both ends; fb_prox_lane.cu: one warp per long range between two fixed points).
+// fb_taut.cuh -- warp-cooperative taut-string search of the team chain-prox kernel k_prox (fb_gfl.cu: two warps per
+// chain from both ends).
 // For the chain v_0..v_{L-1} and tube radius lam the 1-D fused-lasso minimiser (tf_dp_weight, gfl_tf.c:184-321) is the
 // derivative of the taut string through the tube S[k] -+ lam around the prefix sums S.
 #pragma once

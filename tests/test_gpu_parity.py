@@ -114,8 +114,14 @@ def test_cuda_reproduces_golden(gpu_lib, name):
                                                       (100, 1.3, 1e-3, 30000, 0), (64, 0.0, 1e-3, 5, 0),
                                                       (200, 2.5, 1e-12, 120, 0), (200, 2.5, 1e-12, 52, 0),
                                                       (120, 2.0, 1e-3, 30000, 30), (300, 50.0, 1e-4, 30000, 0)])
-def test_gfl_solve_matches_oracle(gpu_lib, oracle, n, lam, conv, maxsteps, md):
-    """The stand-alone fused-lasso solve: same `step`, alpha trajectory, beta / z / u in the reference's slot order."""
+@pytest.mark.parametrize("prox", ["aset", "aset_fallback", "aset_2passes", "team"])
+def test_gfl_solve_matches_oracle(gpu_lib, oracle, monkeypatch, n, lam, conv, maxsteps, md, prox):
+    """The stand-alone fused-lasso solve: same `step`, alpha trajectory, beta / z / u in the reference's slot order.
+    Every variant of the chain prox: the parallel active set (default), its sequential fallback forced for every
+    batch (FB_ASET_MAXPASS=0) or after two passes, and the taut-string team kernel (FB_PROX_ASET=0)."""
+    for k, v in {"aset": {}, "aset_fallback": {"FB_ASET_MAXPASS": "0"}, "aset_2passes": {"FB_ASET_MAXPASS": "2"},
+                 "team": {"FB_PROX_ASET": "0"}}[prox].items():
+        monkeypatch.setenv(k, v)
     rng = np.random.default_rng(n + maxsteps)
     nc = n * (n + 1) // 2
     y = rng.normal(size=nc); w = rng.uniform(0, 3, size=nc); w[rng.random(nc) < 0.2] = 0
@@ -133,6 +139,7 @@ def test_gfl_long_chain_mode_matches_oracle(gpu_lib, oracle, monkeypatch, n, lam
     rng = np.random.default_rng(n)
     nc = n * (n + 1) // 2
     y = rng.normal(size=nc); w = rng.uniform(0, 3, size=nc); w[rng.random(nc) < 0.2] = 0
+    monkeypatch.setenv("FB_PROX_ASET", "0")
     a = gfl_solve(oracle, n, y, w, lam, 1e-4, 30000, 0)
     ref = gfl_solve(gpu_lib, n, y, w, lam, 1e-4, 30000, 0)
     monkeypatch.setenv("FB_PROX_RTAB", str(rtab))
@@ -327,9 +334,13 @@ def test_trail_block_sharding_on_two_gpus():
 
 
 @pytest.mark.timeout(600)
-def test_gfl_global_scratch_default_size_matches_oracle(gpu_lib, oracle):
-    """4300 bins: fewer than six chains fit in shared memory, so the prox kernel keeps the prefix sums in global
-    scratch (15 teams per SM) by default. Eight ADMM iterations against the oracle (~10 s of CPU)."""
+@pytest.mark.parametrize("prox", ["aset", "team"])
+def test_gfl_4300_bins_matches_oracle(gpu_lib, oracle, monkeypatch, prox):
+    """4300 bins, eight ADMM iterations against the oracle (~10 s of CPU). aset: one chain per batch (two CTAs per
+    SM). team: fewer than six chains fit in shared memory, so k_prox keeps the prefix sums in global scratch (15 teams
+    per SM), its default above ~4150 bins."""
+    if prox == "team":
+        monkeypatch.setenv("FB_PROX_ASET", "0")
     n = 4300; nc = n * (n + 1) // 2
     rng = np.random.default_rng(43)
     y = np.repeat(rng.normal(0, 1, nc // 30 + 1), 30)[:nc] + rng.normal(0, 0.5, nc)
