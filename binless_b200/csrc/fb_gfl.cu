@@ -198,7 +198,7 @@ k_prox(Grid g, GflCtl *__restrict__ ctl, const double *__restrict__ beta, const 
        double *__restrict__ zr, double *__restrict__ ur, double *__restrict__ zc, double *__restrict__ uc,
        double *__restrict__ partials, int stride, int rlen, long long *__restrict__ trace,
        const int *__restrict__ list, const int nlist, double *__restrict__ gscratch) {
-    if (ctl->done) return;
+    if (ctl->done || ctl->prox_sel) return;   // prox_sel: this iteration belongs to k_prox_aset
     extern __shared__ double smem[];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int team = wid >> 1, side = wid & 1, bar = 1 + team;
@@ -427,6 +427,7 @@ k_ctl(GflCtl *ctl, const double *__restrict__ partials, int npart, int64_t ncell
         ++step;
         ctl->step = step;
         ctl->next_chain = 0; // work queue of the next k_prox launch
+        ctl->prox_sel = (ctl->aset_from >= 0 && step >= ctl->aset_from) ? 1 : 0;
         const int done = !(step < ctl->maxsteps && cur > ctl->converge);
         ctl->done = done;
         if (GRAPH) cudaGraphSetConditional(cond, done ? 0u : 1u);   // the WHILE node runs the next iteration or stops
@@ -542,6 +543,7 @@ GflSolver::GflSolver(int nbins, unsigned maxdiag, cudaStream_t stream) : nbins_(
         const char *e = std::getenv("FB_PROX_ASET");
         if (!(e && std::atoi(e) == 0) && !trace_.p) aset_plan_build(*aset_, g_, r0_, r1_, c0_, c1_, n_sm_);
         use_aset_ = aset_->usable;
+        if (const char *f = std::getenv("FB_ASET_FROM")) aset_from_ = std::max(1, std::atoi(f));
     }
     // the polling loop stays for the sharded solve (collectives between the kernels) and the trace aid
     use_graph_ = !sharded_ && !trace_.p && st_ != nullptr && !std::getenv("FB_NO_GRAPH");
@@ -687,6 +689,7 @@ GflSolver::~GflSolver() {
 void GflSolver::reset() {
     counter = 0;
     alpha = 5.0;
+    cold_ = true;
     beta_.zero(st_); zr_.zero(st_); ur_.zero(st_); zc_.zero(st_); uc_.zero(st_);
     betaT_.zero(st_);
 }
@@ -697,8 +700,9 @@ void GflSolver::launch_iteration(const double *y, const double *w, bool in_graph
     k_beta<<<tg, tb, 0, st_>>>(g_, ctl_.p, y, w, zr_.p, ur_.p, zc_.p, uc_.p, beta_.p, betaT_.p, r0_, r1_, c0_, c1_);
     tmark(1);
     const int *list = sharded_ ? chain_list_.p : nullptr;
+    // both chain-prox kernels are launched; the one ctl->prox_sel does not name returns at once (k_ctl picks per step:
+    // the taut-string search is faster while the string has few knots, the parallel active set afterwards)
     if (use_aset_) aset_prox_launch(*aset_, ctl_.p, beta_.p, betaT_.p, zr_.p, ur_.p, zc_.p, uc_.p, partials_.p, st_);
-    else
 #define FB_PROX_LAUNCH(LONG_, GS_)                                                                                              \
     k_prox<LONG_, GS_><<<prox_grid_, 64 * prox_warps_, prox_smem_, st_>>>(g_, ctl_.p, beta_.p, betaT_.p, zr_.p, ur_.p, zc_.p, uc_.p,  \
                                                                          partials_.p, prox_stride_, prox_rlen_, trace_.p, list, n_list_, gscratch_.p)
@@ -721,7 +725,7 @@ void GflSolver::launch_iteration(const double *y, const double *w, bool in_graph
 void GflSolver::iteration(const double *y, const double *w, int parity) {
     (void)parity;
     launch_iteration(y, w, false);
-    kernel_launches += 3;
+    kernel_launches += use_aset_ ? 4 : 3;
 }
 
 // One iteration captured into the body of a WHILE conditional node (CUDA >= 12.4). The kernels read y / w from the
@@ -759,6 +763,8 @@ int GflSolver::optimize(const double *d_y_tri, const double *d_w_tri, double lam
     c.presnorm = c.dresnorm = 0; c.step = 1; c.maxsteps = ninner_max;
     c.done = !(c.step < c.maxsteps && (converge + 1) > converge);
     c.rescale = 0; c.next_chain = 0; c.idle = 0;
+    c.aset_from = use_aset_ ? (cold_ ? aset_from_ : 0) : -1;
+    c.prox_sel = (c.aset_from >= 0 && c.step >= c.aset_from) ? 1 : 0;
     c.y = y; c.w = w;
     *h_ctl_ = c;
     FB_CUDA(cudaMemcpyAsync(ctl_.p, h_ctl_, sizeof(GflCtl), cudaMemcpyHostToDevice, st_));
@@ -771,7 +777,7 @@ int GflSolver::optimize(const double *d_y_tri, const double *d_w_tri, double lam
         FB_CUDA(cudaMemcpyAsync(h_ctl_, ctl_.p, sizeof(GflCtl), cudaMemcpyDeviceToHost, st_));
         FB_CUDA(cudaStreamSynchronize(st_));
         if (!h_ctl_->done) throw CudaError("the captured ADMM loop ended without setting done");
-        kernel_launches += 3 * (int64_t)(h_ctl_->step - 1);
+        kernel_launches += (use_aset_ ? 4 : 3) * (int64_t)(h_ctl_->step - 1);
         done = true;
     }
     while (!done) {
@@ -797,6 +803,7 @@ int GflSolver::optimize(const double *d_y_tri, const double *d_w_tri, double lam
         last_steps = h_ctl_->step;
     } else last_steps = 1;
     counter += last_steps;
+    cold_ = false;
     if (sharded_) allgather_rows(beta_.p);   // every rank continues with the whole solution
     if (trapeze_) { // average of the far region (fill_triangle)
         k_band_outside_sums<<<nbins_, 256, 0, st_>>>(g_, nbins_, d_y_tri, d_w_tri, band_partials_.p);
@@ -844,6 +851,7 @@ void GflSolver::import_state(const double *h_beta, const double *h_z, const doub
     FB_CUDA(cudaStreamSynchronize(st_));
     if (h_beta) FB_CUDA(cudaMemcpy(beta_.p, h_beta, N * sizeof(double), cudaMemcpyHostToDevice));
     if (h_z) {
+        cold_ = false;
         FB_CUDA(cudaMemcpy(zr_.p, h_z, (N - 1) * sizeof(double), cudaMemcpyHostToDevice));
         FB_CUDA(cudaMemcpy(zc_.p + 1, h_z + (N - 1), (N - 1) * sizeof(double), cudaMemcpyHostToDevice));
     }

@@ -59,6 +59,8 @@ struct GflCtl {
     int rescale;      // pending dual rescale: 0 none, 1 u /= inflate, 2 u *= inflate
     int next_chain;   // work queue head of k_prox (longest chains first)
     int idle;         // set by k_ctl on launches queued after convergence: the trail-block exchange is skipped
+    int prox_sel;     // chain prox of the NEXT iteration: 0 taut-string team kernel k_prox, 1 parallel active set k_prox_aset
+    int aset_from;    // first step (1-based) that uses k_prox_aset; -1 never
     const double *y, *w;   // inputs of the running solve (the kernels of the captured iteration read them from here)
 };
 
@@ -143,6 +145,8 @@ private:
     // FB_PROX_ASET=0 keeps the taut-string team kernel k_prox (A/B tests)
     std::unique_ptr<AsetPlan> aset_;
     bool use_aset_ = false;
+    int aset_from_ = 13;               // cold start: while the string has few knots the team kernel is faster (B200, 2400 bins: up to step ~13)
+    bool cold_ = true;                 // no solve yet since reset(): the duals carry no knots
     cudaEvent_t ev0_, ev1_;
     // the whole ADMM loop as ONE graph launch: a WHILE conditional node whose body is one iteration, the condition
     // set on the device by k_ctl (no host polling, no launches queued past convergence)

@@ -2,6 +2,7 @@
 // gfl_graph_fl.c:267-365 with tf_dp_weight, gfl_tf.c:184-321). See fb_prox_aset.cu.
 #pragma once
 #include "fb_gfl.cuh"
+#include "fb_prox_aset_passes.cuh"
 #include <vector>
 
 namespace fb {
@@ -19,8 +20,8 @@ struct AsBatch {
     int c0, nch;   // chains [c0, c0 + nch) of the chain table
     int dir;       // 0 rows (beta, z_row, u_row), 1 columns (betaT, z_col, u_col)
     int npts;      // string points in use (multiple of 32)
+    int w0;        // first entry of the batch in the word table
 };
-
 struct AsetPlan {
     bool usable = false;
     int cap = 0;               // string points per batch (multiple of 32)
@@ -29,6 +30,7 @@ struct AsetPlan {
     size_t smem = 0;
     DevBuf<AsChain> chains;
     DevBuf<AsBatch> batches;
+    DevBuf<AsWord> words;
     DevBuf<unsigned long long> stats;   // FB_ASET_STATS development aid
 };
 
