@@ -16,6 +16,9 @@ metric = M cell*iter/s: ADMM cell-iterations of the whole call (sum over fused-l
 identical to the oracle's counts) divided by the time of the whole call.
   value : inputs resident in HBM, results left in HBM (fb_run_signal on an existing handle)
   e2e   : the public API with host buffers: fb_create (validation + H2D) + fb_run_signal + every output column D2H
+e2e_pageable : the same call with pageable numpy buffers and every input column passed (what the Rcpp shim supplies)
+c3_sweep, c4_trailblock : the lambda-grid and trail-block configurations of BASELINE.json, sharded over the N ranks
+         (strong scaling), with the bit-identity of a sharded solve against the single-GPU one (see extra_legs)
 roofline: the ADMM iteration of the fused-lasso solve (the dominant device work), HBM bound, 104 algorithmic
 bytes per cell per iteration, timed with CUDA events on the solver's stream inside the timed steps.
 """
@@ -202,11 +205,26 @@ def run_cuda(args):
     t_e2e = max_over_ranks(time.perf_counter() - t0)
     e2e_value = sum_over_ranks(float(e2e_ci)) / t_e2e / 1e6
 
+    peak, peak_src = measured_peak()
+    # ---- e2e again with what an R caller has: pageable buffers, every input column passed (rank-local, 2 steps) ----
+    pageable = {k: np.array(v, copy=True) for k, v in mat.items()}
+    outp = {k: np.empty_like(v) for k, v in outbuf.items()}
+    def e2e_pageable_step():
+        with lib.create(pageable, n) as hh:
+            return hh.run_signal(ALPHA, LAM2, LAM1, columns=True, buffers=outp)["diagnostics"]["admm_cell_iters"]
+    e2e_pageable_step()
+    barrier()
+    t0 = time.perf_counter()
+    pg_ci = sum(e2e_pageable_step() for _ in range(2))
+    barrier()
+    t_pg = max_over_ranks(time.perf_counter() - t0)
+    pg_value = sum_over_ranks(float(pg_ci)) / t_pg / 1e6
+    del pageable, outp
+    extra = {} if args.no_extra else extra_legs(lib, rank, world, local, peak)
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
-    peak, peak_src = measured_peak()
     sec_per_iter = (ms_solver / 1e3) / max(1, iters)
     achieved = ADMM_BYTES_PER_CELL_ITER * ncells / sec_per_iter / 1e9
     line = {
@@ -218,6 +236,8 @@ def run_cuda(args):
                    "l2": "inputs larger than L2 (working set > 1 GB per call)", "units_per_rank": 1},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
                 "ms_per_step": t_e2e / args.steps * 1e3},
+        "e2e_pageable": {"value": pg_value, "unit": UNIT, "ms_per_step": t_pg / 2 * 1e3, "steps": 2,
+                         "what": "numpy (pageable) host buffers, name / bin1 / bin2 passed and validated: what the Rcpp shim supplies"},
         "gpu_launches": int(launches),
         "clocks": clk,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
@@ -229,11 +249,110 @@ def run_cuda(args):
                      "solver_share_of_device_time": ms_solver / max(ms_dev, 1e-9)},
     }
     # ---- CPU baseline: the oracle on the same workload, one full call, rank 0 only, N = 1 only ------------
+    line.update(extra)
     if world == 1 and not args.no_cpu:
         line["cpu_baseline"] = cpu_baseline(mat, n, full=True)
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def extra_legs(lib, rank, world, local, peak):
+    """The other configurations BASELINE.json names, in the same run (rank 0 reports):
+       c3_sweep      : 64-point lambda2 / BIC sweep of the fitted C2 model, cold-start solves dealt round-robin to the
+                       ranks (strong scaling, no data-path collective; binless_b200/sweep.py)
+       c4_trailblock : ONE fused-lasso solve at 25 000 bins (3.1e8 cells) shared by the ranks through the library's
+                       NCCL communicator (trail blocks, fb_comm_init): ms per ADMM iteration; and whether a sharded
+                       solve equals the single-GPU one bit for bit (3000 bins, 15 steps, both chain-prox kernels)."""
+    import ctypes as C
+    import torch
+    import torch.distributed as dist
+    from binless_b200._abi import _dp, fb_gfl_state, gfl_solve
+    from binless_b200.dist import init_comm, shutdown_comm
+    from binless_b200.shard import partition_units
+    from binless_b200.sweep import lambda_grid
+    out = {}
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def reduce(x, op):
+        if world == 1:
+            return float(x)
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=op)
+        return float(t.item())
+
+    # ---- C3 ------------------------------------------------------------------------------------------------
+    cfg = CONFIGS["C2"]; n, D = cfg["nbins"], cfg["ndatasets"]
+    mat = synth(n, D, cfg["res"], cfg["seed"])                      # the same locus on every rank
+    slim = {k: (None if k in ("name", "bin1", "bin2") else v) for k, v in mat.items()}
+    grid = lambda_grid(64)
+    mine = partition_units(grid.size, world, rank)
+    with lib.create(slim, n) as h:
+        h.run_signal(ALPHA, LAM2, LAM1, columns="none")             # every rank fits the same model (deterministic)
+        h.sweep_lambda(ALPHA, grid[mine][:1], 0.0)                  # warm-up
+        barrier()
+        t0 = time.perf_counter()
+        part = h.sweep_lambda(ALPHA, grid[mine], 0.0)
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+    rows = [(int(u), part["bic"][i].tolist()) for i, u in enumerate(mine)]
+    if world > 1:
+        bucket = [None] * world
+        dist.all_gather_object(bucket, rows)
+        rows = sorted(r for b in bucket for r in b)
+    t_c3 = reduce(dt, dist.ReduceOp.MAX) if world > 1 else dt
+    ci_c3 = reduce(float(part["admm_cell_iters"]), dist.ReduceOp.SUM) if world > 1 else float(part["admm_cell_iters"])
+    bic = np.array([r[1] for r in rows])
+    out["c3_sweep"] = {"workload": f"C3: 64-point lambda2/BIC sweep, {n} bins x {D} datasets, cold-start solves, lambda grid dealt round-robin",
+                       "n_gpus": world, "scaling": "strong", "seconds": t_c3, "Mcell_iter_per_s": ci_c3 / t_c3 / 1e6,
+                       "solves": int(grid.size * D), "best_lam2": grid[np.argmin(bic, axis=0)].tolist()}
+    del mat, slim
+
+    # ---- trail blocks -----------------------------------------------------------------------------------------
+    def fixed_steps(nb, y, w, steps):
+        beta = np.zeros(nb * (nb + 1) // 2)
+        st = fb_gfl_state(beta=_dp(beta), z=None, u=None, alpha=5.0, steps=0)
+        barrier()
+        t = time.perf_counter()
+        lib._check(lib._gfl_solve(nb, 0, _dp(y), _dp(w), 2.5, 1e-12, steps, 0, C.byref(st), None), None)
+        barrier()
+        return time.perf_counter() - t, st.steps, beta
+
+    nchk = 3000; ncc = nchk * (nchk + 1) // 2
+    rng = np.random.default_rng(44)
+    yc = np.repeat(rng.normal(0, 1, ncc // 30 + 1), 30)[:ncc] + rng.normal(0, 0.5, ncc); wc = rng.uniform(0, 3, ncc)
+    single = gfl_solve(lib, nchk, yc, wc, 2.5, 1e-12, 16, 0) if world > 1 else None     # communicator off: this GPU alone
+    nb = CONFIGS["C4"]["nbins"]; nc4 = nb * (nb + 1) // 2
+    rng = np.random.default_rng(4)
+    tile = rng.normal(0, 0.5, 1 << 20)
+    y4 = np.repeat(rng.normal(0, 1, nc4 // 40 + 1), 40)[:nc4]
+    y4 += np.resize(tile, nc4)
+    w4 = np.resize(rng.uniform(0, 3, 1 << 20), nc4)
+    identical = None
+    if world > 1:
+        init_comm(lib)
+        shared = gfl_solve(lib, nchk, yc, wc, 2.5, 1e-12, 16, 0)
+        same = all(np.array_equal(single[k], shared[k]) for k in ("beta", "z", "u", "beta_full")) and \
+            single["steps"] == shared["steps"] and single["alpha"] == shared["alpha"]
+        identical = reduce(0.0 if same else 1.0, dist.ReduceOp.SUM) == 0.0
+    fixed_steps(nb, y4, w4, 2)
+    ta, sa, _ = fixed_steps(nb, y4, w4, 2)
+    tb, sb, _ = fixed_steps(nb, y4, w4, 12)
+    if world > 1:
+        shutdown_comm(lib)
+    per = (tb - ta) / max(1, sb - sa)
+    out["c4_trailblock"] = {"workload": f"C4: one fused-lasso solve, {nb} bins ({nc4} cells), trail blocks over the ranks (fb_comm_init)",
+                            "n_gpus": world, "scaling": "strong", "ms_per_admm_iteration": per * 1e3,
+                            "Mcell_iter_per_s": nc4 / per / 1e6,
+                            "roofline_frac_all_gpus": ADMM_BYTES_PER_CELL_ITER * nc4 / per / 1e9 / (peak * world),
+                            "bit_identical_to_single_gpu": identical,
+                            "bit_identity_check": f"{nchk} bins, 15 ADMM iterations (team kernel, then active set), beta / z / u / steps / alpha"
+                                                  if world > 1 else "n/a at 1 GPU"}
+    return out
 
 
 def cpu_baseline(mat, n, full=True, budget_s=None):
@@ -258,11 +377,9 @@ def run_reference(args):
     if rank != 0:
         return
     cfg = CONFIGS["C2"]
-    n = cfg["nbins"]
-    # bounded sample per step so that (steps + warmup) finishes within a few minutes: the full call is ~16-30 s
-    total = args.steps + args.warmup
-    D = cfg["ndatasets"] if total <= 5 else (2 if total <= 10 else 1)
-    nb = n if total <= 20 else 1200
+    nb, D = cfg["nbins"], cfg["ndatasets"]
+    # every step is one full call on the full C2 workload (the same config as the CUDA arm: ~16 s per call on one
+    # core; the reference has no parallel region on this path)
     mat = synth(nb, D, cfg["res"], cfg["seed"])
     for _ in range(args.warmup):
         cpu_baseline(mat, nb)
@@ -273,11 +390,11 @@ def run_reference(args):
         ci += r["admm_cell_iters"]
     dt = time.perf_counter() - t0
     value = ci / dt / 1e6
-    sample = f"{nb} bins x {D} datasets per step (of the 2400 x 4 workload), full fast_binless call, 1 thread"
+    sample = f"the full workload every step: {nb} bins x {D} datasets, one complete fast_binless call, 1 thread of {os.cpu_count()}"
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": dt / max(1, args.steps) * 1e3, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "sample": sample},
+            "config": {"workload": WORKLOAD, "nbins": nb, "ndatasets": D, "sample": sample},
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": 1, "kind": r["kind"], "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -291,6 +408,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (development)")
+    ap.add_argument("--no-extra", action="store_true", help="skip the C3 / C4 legs (development)")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "cuda":
         args.warmup = 3

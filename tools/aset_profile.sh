@@ -5,7 +5,7 @@ tag=${1:-aset}
 mkdir -p gpurun_out
 FB_NO_GRAPH=1 FB_ASET_STATS=1 timeout 300 python tools/prox_target.py 2400 19 2> gpurun_out/${tag}_stats.log | tail -2
 timeout 300 python tools/prox_target.py 2400 19 | tail -1
-timeout 200 python bench.py --steps 5 --warmup 3 --no-cpu > gpurun_out/${tag}_bench.json 2> gpurun_out/${tag}_bench.err; python -c "
+timeout 200 python bench.py --steps 5 --warmup 3 --no-cpu --no-extra > gpurun_out/${tag}_bench.json 2> gpurun_out/${tag}_bench.err; python -c "
 import json;d=json.load(open('gpurun_out/${tag}_bench.json'));print('bench: ms_per_step',d['ms_per_step'],'us/iter',d['roofline']['us_per_launch'],'frac',d['roofline']['frac'],d['config']['admm_iters_per_solve'])"
 if [ "$2" = "ncu" ]; then
 for skip in 18 25 33; do
