@@ -6,18 +6,23 @@ import collections, csv, io, json, re, subprocess, sys
 def launches(path):
     rows = [r for r in csv.reader(l for l in open(path) if not l.startswith("==")) if r]
     hdr = rows[0]; ix = {h: i for i, h in enumerate(hdr)}
-    tot = collections.OrderedDict()
+    per = collections.OrderedDict()
     for r in rows[1:]:
         if len(r) != len(hdr) or r[ix["Metric Name"]] != "gpu__time_duration.sum":
             continue
         name = re.sub(r"\(.*", "", r[ix["Kernel Name"]]).replace("fb::<unnamed>::", "")
         v = float(r[ix["Metric Value"]].replace(",", "")); u = r[ix["Metric Unit"]]
         v = v / 1e3 if u in ("ns", "nsecond") else v * (1e3 if u in ("ms", "msecond") else 1)
-        c = tot.setdefault(name, [0, 0.0]); c[0] += 1; c[1] += v
-    total = sum(v for _, v in tot.values())
-    for k, (n, v) in sorted(tot.items(), key=lambda kv: -kv[1][1]):
-        print(f"{k:28s} launches {n:4d} total {v:9.1f} us avg {v/n:8.1f} us share {100*v/total:5.1f}%")
-    print(f"total kernel time {total/1e3:.2f} ms")
+        per.setdefault(name, []).append(v)
+    total = sum(sum(v) for v in per.values())
+    # launches that return at once (the chain-prox kernel a step does not use; launches queued past convergence in the
+    # polling loop) would dilute the means: a launch under 10 % of the kernel's longest one counts as "skipped"
+    print(f"{'kernel':34s} {'real':>5s} {'skipped':>7s} {'total us':>10s} {'avg real us':>12s} {'share':>6s}")
+    for k, v in sorted(per.items(), key=lambda kv: -sum(kv[1])):
+        cut = 0.1 * max(v)
+        real = [x for x in v if x >= cut]
+        print(f"{k:34s} {len(real):5d} {len(v) - len(real):7d} {sum(v):10.1f} {sum(real) / len(real):12.1f} {100 * sum(v) / total:5.1f}%")
+    print(f"total kernel time {total/1e3:.2f} ms (cold-cache, serialised by ncu: shares, not absolutes)")
 
 def full(path):
     out = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
