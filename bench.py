@@ -121,7 +121,8 @@ def pinned_empty(n, dtype):
 def run_cuda(args):
     import torch
     import torch.distributed as dist
-    from binless_b200 import cuda_lib, oracle_lib
+    from binless_b200 import cuda_lib
+    from oracle.loader import oracle_lib
 
     rank = int(os.environ.get("RANK", 0)); world = int(os.environ.get("WORLD_SIZE", 1))
     local = int(os.environ.get("LOCAL_RANK", 0))
@@ -358,7 +359,7 @@ def extra_legs(lib, rank, world, local, peak):
 def cpu_baseline(mat, n, full=True, budget_s=None):
     """Times the reference's CPU path (oracle/_ref when built from /root/reference, else the port). 1 thread: the
     reference has no parallel region on this path."""
-    from binless_b200 import oracle_lib
+    from oracle.loader import oracle_lib
     ora = oracle_lib("auto")
     t0 = time.perf_counter()
     with ora.create(mat, n) as h:

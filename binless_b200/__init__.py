@@ -33,19 +33,6 @@ def cuda_lib() -> FastBinlessLib:
     return _lib
 
 
-def oracle_lib(kind: str = "auto") -> FastBinlessLib:
-    """TEST INFRASTRUCTURE: the CPU oracle (oracle/). Only tests, smoke() and bench.py's CPU legs call this."""
-    root = os.path.dirname(_HERE)
-    ref = os.path.join(root, "oracle", "_ref", "libfbo_ref.so")
-    port = os.path.join(root, "oracle", "_build", "libfbo_port.so")
-    if kind == "auto":
-        kind = "reference" if os.path.exists(ref) else "port"
-    path = ref if kind == "reference" else port
-    lib = FastBinlessLib(path, "fbo_")
-    lib.kind = kind
-    return lib
-
-
 def fast_binless(mat, nbins, alpha, lam2, lam1=0.0, nouter=25, tol_val=2e-1, bg_steps=5, free_decay=10000,
                  compute_patchnos=True, csv_out="", maxdiag=0, verbose=False, columns=True):
     """binless:::fast_binless (csnorm_cpp.cpp:18-22 -> fast_binless.cpp:85-184) on the GPU."""

@@ -22,7 +22,7 @@ def _ensure_oracle():
 @pytest.fixture(scope="session")
 def oracle_port():
     _ensure_oracle()
-    from binless_b200 import oracle_lib
+    from oracle.loader import oracle_lib
     return oracle_lib("port")
 
 
@@ -33,13 +33,13 @@ def oracle_ref():
     path = os.path.join(ROOT, "oracle", "_ref", "libfbo_ref.so")
     if not os.path.exists(path):
         pytest.skip("oracle/_ref not built (needs /root/reference at build time)")
-    from binless_b200 import oracle_lib
+    from oracle.loader import oracle_lib
     return oracle_lib("reference")
 
 
 @pytest.fixture(scope="session")
 def oracle(oracle_port):
-    from binless_b200 import oracle_lib
+    from oracle.loader import oracle_lib
     return oracle_lib("auto")
 
 

@@ -89,3 +89,8 @@ def test_product_never_links_the_oracle(product_lib):
     assert "fbo_" not in syms and "gflp_" not in syms
     for f in os.listdir(os.path.join(ROOT, "binless_b200", "csrc")):
         assert "oracle" not in open(os.path.join(ROOT, "binless_b200", "csrc", f)).read().replace("the CPU oracle", ""), f
+    # nor does the Python host side: the loader of the oracle lives in oracle/loader.py, outside the package
+    for f in os.listdir(os.path.join(ROOT, "binless_b200")):
+        if f.endswith(".py"):
+            src = open(os.path.join(ROOT, "binless_b200", f)).read()
+            assert "oracle.loader" not in src and "import oracle" not in src and "libfbo" not in src, f

@@ -41,7 +41,7 @@ def test_bic_identities(oracle_port):
 def _worker(rank, world_size, port, q):
     sys.path.insert(0, ROOT)
     import torch.distributed as dist
-    from binless_b200 import oracle_lib
+    from oracle.loader import oracle_lib
     dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world_size)
     ora = oracle_lib("port")
     mat = synth(N_BINS, N_DS, 5000, SEED)

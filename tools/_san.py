@@ -1,6 +1,7 @@
 import sys, numpy as np
 sys.path.insert(0, '.')
-from binless_b200 import cuda_lib, oracle_lib
+from binless_b200 import cuda_lib
+from oracle.loader import oracle_lib
 from binless_b200._abi import gfl_solve
 lib = cuda_lib()
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 100

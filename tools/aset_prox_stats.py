@@ -31,7 +31,7 @@ def main():
     n = int(sys.argv[1]) if len(sys.argv) > 1 else 600
     iters = int(sys.argv[2]) if len(sys.argv) > 2 else 18
     which = sys.argv[3] if len(sys.argv) > 3 else "both"
-    from binless_b200 import oracle_lib
+    from oracle.loader import oracle_lib
     from binless_b200._abi import gfl_solve
     from binless_b200.synth import synth
     lib = aset_lib()

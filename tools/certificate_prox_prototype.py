@@ -145,7 +145,7 @@ def certified_prox(v, lam, z_prev):
 
 def main():
     n = int(sys.argv[1]) if len(sys.argv) > 1 else 300
-    from binless_b200 import oracle_lib
+    from oracle.loader import oracle_lib
     from binless_b200._abi import gfl_solve
     from binless_b200.synth import synth
     ref = tf_dp_reference()

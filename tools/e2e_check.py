@@ -1,7 +1,8 @@
 """Development check (GPU box): CUDA library vs CPU oracle on full fast_binless / difference / eval_cv runs."""
 import sys, time, numpy as np
 sys.path.insert(0, '.')
-from binless_b200 import cuda_lib, oracle_lib
+from binless_b200 import cuda_lib
+from oracle.loader import oracle_lib
 from binless_b200.synth import synth
 
 gpu, ora = cuda_lib(), oracle_lib()

@@ -7,7 +7,7 @@ import os, sys
 import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
-from binless_b200 import oracle_lib
+from oracle.loader import oracle_lib
 from binless_b200.synth import synth
 
 CASES = {
