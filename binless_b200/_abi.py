@@ -65,6 +65,10 @@ class fb_sweep_out(C.Structure):
                 ("admm_cell_iters", C.c_int64)]
 
 
+class fb_cv_score_out(C.Structure):
+    _fields_ = [("cv", c_dp), ("cv_sd", c_dp), ("steps", c_ip), ("ms_solver", C.c_double), ("admm_cell_iters", C.c_int64)]
+
+
 class fb_gfl_state(C.Structure):
     _fields_ = [("beta", c_dp), ("z", c_dp), ("u", c_dp), ("alpha", C.c_double), ("steps", C.c_int)]
 
@@ -72,7 +76,7 @@ class fb_gfl_state(C.Structure):
 ENTRY_POINTS = ["create", "destroy", "last_error", "run_signal", "restore", "run_difference",
                 "eval_cv", "sweep_lambda", "gfl_solve", "set_interrupt_cb", "kernel_launches", "release_cached_memory",
                 "comm_unique_id", "comm_init", "comm_destroy", "comm_rank", "comm_world", "shard_plan",
-                "create_binned", "get_mat", "mat_rows"]
+                "create_binned", "get_mat", "mat_rows", "cv_score", "csv_write"]
 
 
 def _dp(a):
@@ -138,6 +142,12 @@ class FastBinlessLib:
         self._sweep_lambda = f("sweep_lambda")
         self._sweep_lambda.argtypes = [C.c_void_p, C.POINTER(fb_params), C.c_int, c_dp, C.POINTER(fb_sweep_out)]
         self._sweep_lambda.restype = C.c_int
+        self._cv_score = f("cv_score")
+        self._cv_score.argtypes = [C.c_void_p, C.POINTER(fb_params), C.c_int, c_dp, C.POINTER(fb_cv_score_out)]
+        self._cv_score.restype = C.c_int
+        self._csv_write = f("csv_write")
+        self._csv_write.argtypes = [C.c_char_p, C.c_char_p, C.c_int64, C.c_int, C.POINTER(c_dp), C.c_int]
+        self._csv_write.restype = C.c_int
         self._kernel_launches = f("kernel_launches")
         self._kernel_launches.argtypes = [C.c_void_p]; self._kernel_launches.restype = C.c_int64
         self._gfl_solve = f("gfl_solve")
@@ -154,6 +164,12 @@ class FastBinlessLib:
         self._comm_destroy = f("comm_destroy"); self._comm_destroy.argtypes = []; self._comm_destroy.restype = C.c_int
         self._shard_plan = f("shard_plan")
         self._shard_plan.argtypes = [C.c_int, C.c_uint, C.c_int, c_ip, c_ip]; self._shard_plan.restype = C.c_int
+
+    def csv_write(self, path, header, cols, gzip=True):
+        """The reference's csvfile for caller-owned columns (fb_csv_write): gzip as built, or plain text."""
+        cols = [_f64(c) for c in cols]
+        arr = (c_dp * len(cols))(*[_dp(c) for c in cols])
+        self._check(self._csv_write(str(path).encode(), header.encode(), int(cols[0].size), len(cols), arr, int(bool(gzip))), None)
 
     # ---- multi-GPU (one process per GPU) --------------------------------
     def shard_plan(self, nbins, world, maxdiag=0):
@@ -345,6 +361,22 @@ class Handle:
         self.lib._check(rc, self.h)
         return {"lam2": lam2a, "bic": bic, "chisq": chisq, "dof": dof, "steps": steps, "ms_solver": o.ms_solver,
                 "admm_cell_iters": int(o.admm_cell_iters)}
+
+
+def _cv_score_impl(self, alpha, lam2, lam1=0.0, tol_val=0.2, maxdiag=0):
+    """Checkerboard CV score per (lambda2, dataset) (fb_cv_score): cv, cv_sd of shape (len(lam2), ndatasets)."""
+    lam2a = _f64(np.atleast_1d(lam2))
+    p = self.lib._params(alpha, lam2a[:1] if lam2a.size else [0.0], lam1, tol_val=tol_val, maxdiag=maxdiag)
+    shape = (lam2a.size, self.ndatasets)
+    cv = np.empty(shape); sd = np.empty(shape); steps = np.empty(shape + (2,), dtype=np.int32)
+    o = fb_cv_score_out(cv=_dp(cv), cv_sd=_dp(sd), steps=_ip(steps))
+    rc = self.lib._cv_score(self.h, C.byref(p), lam2a.size, _dp(lam2a), C.byref(o))
+    self.lib._check(rc, self.h)
+    return {"lam2": lam2a, "cv": cv, "cv_sd": sd, "steps": steps, "ms_solver": o.ms_solver,
+            "admm_cell_iters": int(o.admm_cell_iters)}
+
+
+Handle.cv_score = _cv_score_impl
 
 
 def gfl_solve(lib: FastBinlessLib, nbins, y, w, lam2, converge, maxsteps=30000, maxdiag=0, state=None):

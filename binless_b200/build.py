@@ -78,7 +78,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
                     print(log, file=sys.stderr)
     if jobs or not os.path.exists(LIB):
         cmd = [NVCC, "-shared", "-o", LIB, *objs, "-gencode", "arch=compute_100a,code=sm_100a",
-               "-Xcompiler", "-fPIC", "-lcudart_static", "-lpthread", "-ldl", "-lrt"]
+               "-Xcompiler", "-fPIC", "-lcudart_static", "-lpthread", "-ldl", "-lrt", "-lz"]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")

@@ -3,6 +3,7 @@
 // mirror (binless_b200/_abi.py) bind exactly these symbols.
 #include "fb_model.cuh"
 #include "fb_comm.cuh"
+#include "fb_csv.hpp"
 #include <string>
 
 struct fb_handle {
@@ -74,6 +75,18 @@ FB_API int fb_eval_cv(fb_handle *h, const fb_params *p, int nlam, const double *
 FB_API int fb_sweep_lambda(fb_handle *h, const fb_params *p, int nlam, const double *lam2, fb_sweep_out *out) {
     if (!h) { fb::g_last_error = "null handle"; return FB_ERR_ARG; }
     return guarded(h->m.err, [&] { h->m.sweep_lambda(p, nlam, lam2, out); });
+}
+
+FB_API int fb_cv_score(fb_handle *h, const fb_params *p, int nlam, const double *lam2, fb_cv_score_out *out) {
+    if (!h) { fb::g_last_error = "null handle"; return FB_ERR_ARG; }
+    return guarded(h->m.err, [&] { h->m.cv_score(p, nlam, lam2, out); });
+}
+
+FB_API int fb_csv_write(const char *path, const char *header, int64_t nrows, int ncols, const double *const *cols, int gzip) {
+    if (!path || !header || nrows < 0 || ncols <= 0 || !cols) { fb::g_last_error = "bad argument"; return FB_ERR_ARG; }
+    return guarded(fb::g_last_error, [&] {
+        if (!fb::write_csv_gz(path, header, nrows, ncols, cols, gzip != 0)) throw fb::ArgError(std::string("cannot write ") + path);
+    });
 }
 
 FB_API int fb_set_interrupt_cb(fb_handle *h, int (*cb)(void *), void *arg) {

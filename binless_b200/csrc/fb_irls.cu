@@ -9,11 +9,23 @@ namespace {
 constexpr int EW_THREADS = 256, EW_PER_THREAD = 4, EW_SPAN = EW_THREADS * EW_PER_THREAD;
 
 // get_log_expected for one cell (fast_expected.ipp:1-19): ((bias + decay) + signal) + exposure, with the
-// bias term the sum of the two selector entries (fast_bias_mean.hpp:50-52)
-__device__ __forceinline__ double log_expected(const LegTables &L, int i, int j, int d, double phi) {
-    const double bi = L.brow[i];
-    const double b = (i == j) ? 2. * bi : bi + L.brow[j];
-    return ((b + L.ddiag[j - i]) + phi) + L.expo[d];
+// bias term the sum of the two selector entries (fast_bias_mean.hpp:50-52). bias_decay(): the two table terms, from the
+// closed-form tables (bin_data layout) or, in the per-cell fallback (L.cb1 set), through the int32 bin indices of the cell.
+__device__ __forceinline__ void bias_decay(const LegTables &L, int i, int j, int64_t idx, double &b, double &dc) {
+    if (L.cb1) {
+        const int p = L.cb1[idx], q = L.cb2[idx];
+        b = (p == q) ? 2. * L.brow[p] : (p < q ? L.brow[p] + L.brow[q] : L.brow[q] + L.brow[p]);
+        dc = L.ddiag[L.cdb[idx]];
+    } else {
+        const double bi = L.brow[i];
+        b = (i == j) ? 2. * bi : bi + L.brow[j];
+        dc = L.ddiag[j - i];
+    }
+}
+__device__ __forceinline__ double log_expected(const LegTables &L, int i, int j, int d, int64_t idx, double phi) {
+    double b, dc;
+    bias_decay(L, i, j, idx, b, dc);
+    return ((b + dc) + phi) + L.expo[d];
 }
 
 // NB working residual and weight (fast_residuals.ipp:47-67)
@@ -94,7 +106,7 @@ k_leg_pass(Tri t, LegTables L, double alpha, const int32_t *__restrict__ obs, co
             if (ok[q]) {
                 if (MODE == MODE_NOBS) { a = (double)no[q]; }
                 else {
-                    const double eta = log_expected(L, i, j, d, ph[q]);
+                    const double eta = log_expected(L, i, j, d, base + rm_start(i, n) + (j - i), ph[q]);
                     if (MODE == MODE_RESID) {
                         double z, w;
                         nb_residual(eta, ob[q], no[q], alpha, z, w);
@@ -234,7 +246,7 @@ k_signal_yw(Tri t, LegTables L, double alpha, const int32_t *__restrict__ obs, c
         const int64_t idx = rowbase + off;
         const double ph = phi[idx];
         double z, wt;
-        nb_residual(log_expected(L, i, j, d, ph), obs[idx], nobs[idx], alpha, z, wt);
+        nb_residual(log_expected(L, i, j, d, idx, ph), obs[idx], nobs[idx], alpha, z, wt);
         // checkerboard hold-out on 1-based bins (fast_binless.ipp:14-22)
         const unsigned cvgroup = 1 + ((unsigned)((j + 1) + (i + 1)) % 2);
         if (cvgroup == group) { y[idx] = -100; w[idx] = 0; }
@@ -255,8 +267,8 @@ k_precision(Tri t, LegTables Lo, LegTables Ln, const double *__restrict__ phi_ol
         for (int off = threadIdx.x; off < n - i; off += EW_THREADS) {
             const int j = i + off;
             const int64_t idx = rowbase + off;
-            const double eo = log_expected(Lo, i, j, d, phi_old[idx]);
-            const double en = log_expected(Ln, i, j, d, phi_new[idx]);
+            const double eo = log_expected(Lo, i, j, d, idx, phi_old[idx]);
+            const double en = log_expected(Ln, i, j, d, idx, phi_new[idx]);
             dabs = fmax(dabs, fabs(en - eo));
             mx = fmax(mx, en); mn = fmin(mn, en);
         }
@@ -398,9 +410,8 @@ k_output_signal(Tri t, LegTables L, const int32_t *__restrict__ nobs, const doub
                 double *__restrict__ decaymat, double *__restrict__ signal, double *__restrict__ binless) {
     EW_FOREACH_CELL(t) {
         const int64_t idx = rowbase + off;
-        const double bi = L.brow[i];
-        const double bipbj = (i == j) ? 2. * bi : bi + L.brow[j];
-        const double ldec = L.ddiag[j - i];
+        double bipbj, ldec;
+        bias_decay(L, i, j, idx, bipbj, ldec);
         const double l1 = lam1[d];
         double lsig = phi[idx];
         lsig = (lsig > 0) ? fmax(0., lsig - l1) : fmin(0., lsig + l1); // soft_threshold, util.cpp:8-18
@@ -422,7 +433,7 @@ k_diff_prepare(Tri t, LegTables L, double alpha, const int32_t *__restrict__ obs
         // FastData<Difference>: log_difference = log_signal - phi_ref, log_signal = phi_ref + log_difference (FastData.cpp:6-31)
         const double dsig = pref + (phi[idx] - pref);
         double z, wt;
-        nb_residual(log_expected(L, i, j, d, dsig), obs[idx], nobs[idx], alpha, z, wt);
+        nb_residual(log_expected(L, i, j, d, idx, dsig), obs[idx], nobs[idx], alpha, z, wt);
         const double ph = z + dsig;
         phihat[idx] = ph; deltahat[idx] = ph - pref; w[idx] = wt;
     }
@@ -560,6 +571,81 @@ __global__ void k_fill_i32(int32_t *p, int64_t n, int32_t v) {
     if (i < n) p[i] = v;
 }
 
+
+// --------------------------------------------------------------------------
+// per-cell fallback of the bias / decay leg passes (inputs whose pos / distance are not functions of the
+// bin / diagonal, binned cell by cell like util.cpp:56-111): the pair (a, b) of every cell, then one warp per leg bin
+// sums the cells of its list (ascending cell order, lane-strided, butterfly: a fixed shape, same bits on every run)
+// --------------------------------------------------------------------------
+template <int MODE>
+__global__ void __launch_bounds__(EW_THREADS)
+k_cell_ab(Tri t, LegTables L, double alpha, const int32_t *__restrict__ obs, const int32_t *__restrict__ nobs,
+          const double *__restrict__ phi, double *__restrict__ ca, double *__restrict__ cb) {
+    EW_FOREACH_CELL(t) {
+        const int64_t idx = rowbase + off;
+        double a = 0.0, b = 0.0;
+        const int no = nobs[idx];
+        if (MODE == MODE_NOBS) a = (double)no;
+        else {
+            const double eta = log_expected(L, i, j, d, idx, phi[idx]);
+            if (MODE == MODE_RESID) { double z, w; nb_residual(eta, obs[idx], no, alpha, z, w); a = w; b = z * w; }
+            else { a = (double)obs[idx]; b = exp(eta) * (double)no; }
+        }
+        ca[idx] = a; cb[idx] = b;
+    }
+}
+// list entry = cell index, bit 31 set when the cell counts twice (both selector entries of the bias binner in this bin)
+__global__ void __launch_bounds__(128)
+k_bin_sum(int nb, const int64_t *__restrict__ off, const uint32_t *__restrict__ list, const double *__restrict__ ca,
+          const double *__restrict__ cb, double *__restrict__ items) {
+    const int bin = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (bin >= nb) return;
+    double a = 0.0, b = 0.0;
+    for (int64_t k = off[bin] + lane; k < off[bin + 1]; k += 32) {
+        const uint32_t e = list[k];
+        const uint32_t c = e & 0x7fffffffu;
+        const double m = (e >> 31) ? 2.0 : 1.0;
+        a += m * ca[c]; b += m * cb[c];
+    }
+    a = warp_sum(a); b = warp_sum(b);
+    if (lane == 0) { items[2 * bin] = a; items[2 * bin + 1] = b; }
+}
+
+// checkerboard cross-validation: sum and count of chisq = w (phihat - soft(beta, lam1))^2 + lam1^2 over the cells of
+// group g = (bin1 + bin2) % 2 (ScorePreparator.ipp:8-16, Likelihoods.hpp:25-42 with eCprime = 0); one partial per block
+__global__ void __launch_bounds__(EW_THREADS)
+k_cv_group_sum(int n, int g, const double *__restrict__ phihat, const double *__restrict__ w, const double *__restrict__ beta,
+               double lam1, double *__restrict__ partial) {
+    __shared__ double s[32];
+    double acc = 0.0, cnt = 0.0;
+    for (int i = blockIdx.x; i < n; i += gridDim.x) {
+        const int64_t rowbase = rm_start(i, n);
+        for (int off = threadIdx.x; off < n - i; off += EW_THREADS) {
+            const int j = i + off;
+            if ((((i + 1) + (j + 1)) & 1) != g) continue;
+            const int64_t idx = rowbase + off;
+            const double b = beta[idx];
+            const double soft = b > 0 ? fmax(0., b - lam1) : fmin(0., b + lam1);
+            const double dd = phihat[idx] - soft;
+            acc += w[idx] * (dd * dd) + lam1 * lam1;
+            cnt += 1.0;
+        }
+    }
+    const double ra = block_sum(acc, s);
+    const double rc = block_sum(cnt, s);
+    if (threadIdx.x == 0) { partial[2 * blockIdx.x] = ra; partial[2 * blockIdx.x + 1] = rc; }
+}
+__global__ void __launch_bounds__(1024)
+k_cv_fin(int nblocks, const double *__restrict__ partial, double *__restrict__ out2) {
+    __shared__ double s[32];
+    double a = 0.0, c = 0.0;
+    for (int k = threadIdx.x; k < nblocks; k += blockDim.x) { a += partial[2 * k]; c += partial[2 * k + 1]; }
+    const double ra = block_sum(a, s);
+    const double rc = block_sum(c, s);
+    if (threadIdx.x == 0) { out2[0] = ra; out2[1] = rc; }
+}
+
 inline dim3 ew_grid(const Tri &t) { return dim3((unsigned)((t.n + EW_SPAN - 1) / EW_SPAN), (unsigned)t.n, (unsigned)t.D); }
 inline dim3 tile_grid(const Tri &t) { return dim3((unsigned)tiles_j(t.n), (unsigned)tiles_i(t.n), (unsigned)t.D); }
 
@@ -595,6 +681,25 @@ void leg_pass(int leg, int mode, const Tri &t, LegTables L, double alpha, const 
         leg_pass_mode<LEG_DECAY>(mode, t, L, alpha, obs, nobs, phi, part, st);
         k_fin_decay<<<(t.n + 3) / 4, 128, 0, st>>>(t, ntI, ntJ, part, items);
     }
+    FB_LAUNCH_CHECK();
+}
+
+
+void leg_pass_cells(int mode, const Tri &t, LegTables L, double alpha, const int32_t *obs, const int32_t *nobs, const double *phi,
+                    int nb, const int64_t *off, const uint32_t *list, double *ca, double *cb, double *items, cudaStream_t st) {
+    switch (mode) {
+    case MODE_RESID: k_cell_ab<MODE_RESID><<<ew_grid(t), EW_THREADS, 0, st>>>(t, L, alpha, obs, nobs, phi, ca, cb); break;
+    case MODE_POISSON: k_cell_ab<MODE_POISSON><<<ew_grid(t), EW_THREADS, 0, st>>>(t, L, alpha, obs, nobs, phi, ca, cb); break;
+    default: k_cell_ab<MODE_NOBS><<<ew_grid(t), EW_THREADS, 0, st>>>(t, L, alpha, obs, nobs, phi, ca, cb); break;
+    }
+    k_bin_sum<<<(nb + 3) / 4, 128, 0, st>>>(nb, off, list, ca, cb, items);
+    FB_LAUNCH_CHECK();
+}
+
+void cv_group_sum(int n, int g, const double *phihat, const double *w, const double *beta, double lam1, double *partial,
+                  double *out2, cudaStream_t st) {
+    k_cv_group_sum<<<CV_BLOCKS, EW_THREADS, 0, st>>>(n, g, phihat, w, beta, lam1, partial);
+    k_cv_fin<<<1, 1024, 0, st>>>(CV_BLOCKS, partial, out2);
     FB_LAUNCH_CHECK();
 }
 

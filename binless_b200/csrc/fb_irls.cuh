@@ -35,6 +35,9 @@ struct LegTables {
     const double *brow;   // [n]  binned bias estimate per row/column index
     const double *ddiag;  // [n]  binned decay estimate per diagonal
     const double *expo;   // [D]  binned exposure estimate per dataset
+    // per-cell fallback: when cb1 is set, brow is indexed by BIAS BIN and ddiag by DECAY BIN, and every
+    // cell carries the int32 bins of pos1 / pos2 / log(distance) (util.cpp:56-111 semantics); else null
+    const int32_t *cb1 = nullptr, *cb2 = nullptr, *cdb = nullptr;
 };
 
 enum { LEG_EXPO = 0, LEG_BIAS = 1, LEG_DECAY = 2 };
@@ -56,6 +59,17 @@ size_t leg_part_doubles(const Tri &t);
 // Fixed-shape reduction: same bits on every run.
 void leg_pass(int leg, int mode, const Tri &t, LegTables L, double alpha, const int32_t *obs, const int32_t *nobs,
               const double *phi, double *part, double *items, cudaStream_t st);
+
+// The same sums in the per-cell fallback, for the bias / decay leg: `off` / `list` are the CSR cell lists of the nb leg bins
+// (bit 31 of an entry: the cell counts twice), ca / cb two N-double scratch arrays; items[2*bin], items[2*bin+1].
+void leg_pass_cells(int mode, const Tri &t, LegTables L, double alpha, const int32_t *obs, const int32_t *nobs, const double *phi,
+                    int nb, const int64_t *off, const uint32_t *list, double *ca, double *cb, double *items, cudaStream_t st);
+
+// checkerboard CV: out2 = {sum of chisq, number of cells} over the cells of group g = (bin1 + bin2) % 2 of one dataset;
+// partial: 2 * CV_BLOCKS doubles of scratch
+constexpr int CV_BLOCKS = 592;
+void cv_group_sum(int n, int g, const double *phihat, const double *w, const double *beta, double lam1, double *partial,
+                  double *out2, cudaStream_t st);
 
 // y = z + phi, w (step_signal, fast_binless.ipp:13-23); group = CV hold-out (0 = none)
 void signal_yw(const Tri &t, LegTables L, double alpha, const int32_t *obs, const int32_t *nobs, const double *phi,

@@ -1,5 +1,6 @@
 // fb_model.cu -- host driver of the fast-binless path (see fb_model.cuh).
 #include "fb_model.cuh"
+#include "fb_csv.hpp"
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
@@ -13,7 +14,7 @@
 
 namespace fb {
 
-std::string g_last_error;
+thread_local std::string g_last_error;   // per host thread: handles may be created from several threads
 
 namespace {
 
@@ -27,6 +28,7 @@ struct PhaseTimer {
 };
 PhaseTimer g_pt;
 
+const char *kLayoutMsg = "pos1/pos2 do not depend on the bin only or distance not on bin2-bin1 only";   // -> per-cell fallback
 const char *kSizeMsg = "Input size should be N(N+1)/2 dense matrix of observed counts for each dataset";
 
 // make_even_bins + bin_data with drop=true (util.cpp:56-111): bin index of each value, unused bins removed
@@ -55,35 +57,12 @@ std::vector<double> broadcast(const double *p, int np, int n) {
     return std::vector<double>(n, p[0]);
 }
 
-// csvfile of the reference (csvfile.hpp:30-117, USE_BOOST = 0): quoted header, then one row per cell with every value
-// printed as std::fixed << std::setprecision(4), comma separated (fast_dataframe.cpp:23-57). Rows are formatted by
-// several host threads, slab by slab, and written in order.
+// csv_out (fast_dataframe.cpp:23-57): gzip like the reference as built (USE_BOOST = 1, Makevars:1-2; csvfile.hpp:46-48);
+// FB_CSV_PLAIN=1 writes the plain text of a USE_BOOST = 0 build
 void write_signal_csv(const char *path, int64_t N, const double *const cols[7]) {
-    FILE *f = std::fopen(path, "w");
-    if (!f) { std::printf("Exception creating csv file: cannot open %s\n", path); return; } // the reference only reports it
-    std::fputs("\"phihat\",\"weight\",\"biasmat\",\"decaymat\",\"signal\",\"binless\",\"background\"\n", f);
-    const int nthr = (int)std::min(16u, std::max(1u, std::thread::hardware_concurrency()));
-    const int64_t slab = 1 << 20;
-    std::vector<std::string> parts(nthr);
-    for (int64_t base = 0; base < N; base += slab) {
-        const int64_t cnt = std::min<int64_t>(slab, N - base);
-        std::vector<std::future<void>> fut;
-        for (int t = 0; t < nthr; ++t)
-            fut.push_back(std::async(std::launch::async, [&, t] {
-                const int64_t lo = base + cnt * t / nthr, hi = base + cnt * (t + 1) / nthr;
-                std::string &o = parts[t];
-                o.clear(); o.reserve((size_t)(hi - lo) * 64);
-                char buf[512];
-                for (int64_t i = lo; i < hi; ++i) {
-                    const int len = std::snprintf(buf, sizeof buf, "%.4f,%.4f,%.4f,%.4f,%.4f,%.4f,%.4f\n", cols[0][i], cols[1][i],
-                                                  cols[2][i], cols[3][i], cols[4][i], cols[5][i], cols[6][i]);
-                    o.append(buf, (size_t)std::min<int>(len, (int)sizeof buf - 1));
-                }
-            }));
-        for (auto &x : fut) x.get();
-        for (int t = 0; t < nthr; ++t) std::fwrite(parts[t].data(), 1, parts[t].size(), f);
-    }
-    std::fclose(f);
+    const char *e = std::getenv("FB_CSV_PLAIN");
+    write_csv_gz(path, "\"phihat\",\"weight\",\"biasmat\",\"decaymat\",\"signal\",\"binless\",\"background\"", N, 7, cols,
+                 !(e && std::atoi(e) != 0));
 }
 
 // copies of at least this many bytes to / from pageable host memory are pipelined through pinned staging
@@ -106,24 +85,31 @@ int host_threads() {
 // ---------------------------------------------------------------------------------------------
 // ingest: FastDataCore (FastData.ipp:3-26) + verification of the bin_data layout
 // ---------------------------------------------------------------------------------------------
-Model::Model(int nbins, const fb_mat *mat) {
+void Model::open_stream() {
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
         throw CudaError("no CUDA device available (there is no CPU fallback)");
     FB_CUDA(cudaStreamCreateWithFlags(&st_, cudaStreamNonBlocking));
     FB_CUDA(cudaEventCreate(&ev0_));
     FB_CUDA(cudaEventCreate(&ev1_));
-    ingest(nbins, mat);
+}
+void Model::close_stream() {
+    if (st_) cudaStreamSynchronize(st_); // buffers go back to the block cache only when nothing uses them any more
+    if (ev0_) cudaEventDestroy(ev0_);
+    if (ev1_) cudaEventDestroy(ev1_);
+    if (st_) cudaStreamDestroy(st_);
+    st_ = nullptr; ev0_ = ev1_ = nullptr;
+}
+
+// a constructor that throws (rejected input: the normal validation path) does not run the destructor
+Model::Model(int nbins, const fb_mat *mat) {
+    open_stream();
+    try { ingest(nbins, mat); } catch (...) { close_stream(); throw; }
 }
 
 Model::Model(const fb_reads *reads, int *nbins_out) {
-    int ndev = 0;
-    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
-        throw CudaError("no CUDA device available (there is no CPU fallback)");
-    FB_CUDA(cudaStreamCreateWithFlags(&st_, cudaStreamNonBlocking));
-    FB_CUDA(cudaEventCreate(&ev0_));
-    FB_CUDA(cudaEventCreate(&ev1_));
-    ingest_reads(reads, nbins_out);
+    open_stream();
+    try { ingest_reads(reads, nbins_out); } catch (...) { close_stream(); throw; }
 }
 
 // the per-handle work buffers that do not depend on how the matrix arrived
@@ -131,9 +117,7 @@ void Model::alloc_work() {
     const int64_t n = t_.n, D = t_.D, N = D * t_.ncells;
     phi_.alloc(N); phi_new_.alloc(N); phihat_.alloc(N); wgt_.alloc(N);
     phi_.zero(st_); phihat_.zero(st_); wgt_.zero(st_);
-    tab_.alloc(2 * (size_t)n + D); tab_old_.alloc(2 * (size_t)n + D);
-    tab_h_.alloc(2 * (size_t)n + D);
-    items_.alloc(2 * (size_t)std::max<int64_t>(n, D)); items_h_.alloc(2 * (size_t)std::max<int64_t>(n, D));
+    alloc_tables();
     prec_h_.alloc(4);
     part_.alloc(leg_part_doubles(t_));
     scratch_.alloc(4096);
@@ -141,12 +125,17 @@ void Model::alloc_work() {
     FB_CUDA(cudaStreamSynchronize(st_));
 }
 
-Model::~Model() {
-    if (st_) cudaStreamSynchronize(st_); // buffers go back to the block cache only when nothing uses them any more
-    if (ev0_) cudaEventDestroy(ev0_);
-    if (ev1_) cudaEventDestroy(ev1_);
-    if (st_) cudaStreamDestroy(st_);
+// device / pinned leg tables [bias part | decay part | exposures] and the per-item sums of one leg pass
+void Model::alloc_tables() {
+    const int64_t n = t_.n, D = t_.D;
+    if (!generic_) { tab_b_ = (int)n; tab_d_ = (int)n; }
+    const size_t tn = (size_t)tab_b_ + tab_d_ + D;
+    tab_.alloc(tn); tab_old_.alloc(tn); tab_h_.alloc(tn);
+    const size_t items = 2 * (size_t)std::max<int64_t>(std::max<int64_t>(n, D), std::max(tab_b_, tab_d_));
+    items_.alloc(items); items_h_.alloc(items);
 }
+
+Model::~Model() { close_stream(); }
 
 void Model::ingest(int nbins, const fb_mat *m) {
     if (!m || m->N <= 0 || nbins <= 0) throw ArgError("empty input");
@@ -216,7 +205,7 @@ void Model::ingest(int nbins, const fb_mat *m) {
             for (int64_t j = i; j < n; ++j) {
                 const int64_t g = base + (j - i);
                 if ((double)m->pos1[g] != pi || (double)m->pos2[g] != pos_[j] || m->distance[g] != dist_[j - i])
-                    return "pos1/pos2 must depend on the bin only and distance on bin2-bin1 only (bin_data layout, R/preprocess.R:104-148)";
+                    return kLayoutMsg;
             }
             return nullptr;
         });
@@ -226,9 +215,6 @@ void Model::ingest(int nbins, const fb_mat *m) {
     { // same buffers as alloc_work(), without its synchronisation: the validation below overlaps the uploads
         phi_.alloc(N); phi_new_.alloc(N); phihat_.alloc(N); wgt_.alloc(N);
         phi_.zero(st_); phihat_.zero(st_); wgt_.zero(st_);
-        tab_.alloc(2 * (size_t)n + D); tab_old_.alloc(2 * (size_t)n + D);
-        tab_h_.alloc(2 * (size_t)n + D);
-        items_.alloc(2 * (size_t)std::max<int64_t>(n, D)); items_h_.alloc(2 * (size_t)std::max<int64_t>(n, D));
         prec_h_.alloc(4);
         part_.alloc(leg_part_doubles(t_));
         scratch_.alloc(4096);
@@ -236,9 +222,119 @@ void Model::ingest(int nbins, const fb_mat *m) {
     }
     const char *e = checks.get();
     FB_CUDA(cudaStreamSynchronize(st_));
-    if (e) throw ArgError(e);
-    for (int64_t k = 0; k < n; ++k)
-        if (!(dist_[k] > 0)) throw ArgError("distance must be positive");
+    if (e == kLayoutMsg || std::getenv("FB_FORCE_CELL_BINS")) {
+        // not a bin_data() layout (or the test aid asks for it): bin every cell like the reference does (util.cpp:56-111)
+        if (e && e != kLayoutMsg) throw ArgError(e);
+        ingest_cells(m);
+    } else {
+        if (e) throw ArgError(e);
+        for (int64_t k = 0; k < n; ++k)
+            if (!(dist_[k] > 0)) throw ArgError("distance must be positive");
+    }
+    alloc_tables();
+}
+
+namespace {
+// make_even_bins (util.cpp:56-68) as a sorted edge list: (edge value, index); equal edges keep the LAST index like the
+// std::map assignment of the reference
+struct EvenBins {
+    std::vector<double> key; std::vector<unsigned> val; unsigned Nbins;
+    EvenBins(double lower, double upper, unsigned Nb) : Nbins(Nb) {
+        std::map<double, unsigned> edges;
+        const double size = upper - lower;
+        for (unsigned i = 0; i <= Nb; ++i) edges[lower + i * size / double(Nb)] = i;
+        for (auto &kv : edges) { key.push_back(kv.first); val.push_back(kv.second); }
+    }
+    int bin(double v) const {   // bin_data (util.cpp:70-81): upper_bound, past the end -> last bin
+        const size_t k = std::upper_bound(key.begin(), key.end(), v) - key.begin();
+        return (int)((k == key.size() ? val.back() : val[k]) - 1);
+    }
+};
+template <class F>
+void par_for(int64_t N, F &&fn) {   // fn(lo, hi) on host_threads() contiguous ranges
+    const int nthr = host_threads();
+    std::vector<std::thread> th;
+    for (int t = 1; t < nthr; ++t) th.emplace_back([&, t] { fn(N * t / nthr, N * (t + 1) / nthr); });
+    fn(0, N / nthr);
+    for (auto &x : th) x.join();
+}
+// drop = true (util.cpp:83-98): bins nobody uses are removed; returns the number kept
+int drop_unused(std::vector<int32_t> &raw, unsigned Nbins) {
+    std::vector<char> used(Nbins, 0);
+    for (int32_t r : raw) used[r] = 1;
+    std::vector<int32_t> remap(Nbins, -1);
+    int kept = 0;
+    for (unsigned b = 0; b < Nbins; ++b) if (used[b]) remap[b] = kept++;
+    par_for((int64_t)raw.size(), [&](int64_t lo, int64_t hi) { for (int64_t k = lo; k < hi; ++k) raw[k] = remap[raw[k]]; });
+    return kept;
+}
+} // namespace
+
+// Per-cell binners of the bias and decay legs (fast_bias_mean.hpp:37-68, fast_decay.hpp:48-68 over util.cpp:56-111),
+// evaluated for every cell with the reference's double expressions; the cell lists per leg bin feed leg_pass_cells.
+void Model::ingest_cells(const fb_mat *m) {
+    const int64_t N = m->N;
+    if (N >= (int64_t(1) << 31)) throw ArgError("the per-cell binner fallback supports fewer than 2^31 cells");
+    generic_ = true;
+    const int n = t_.n;
+    // bias: even bins between the smallest and the largest position of either end
+    double mn = INFINITY, mx = -INFINITY;
+    for (int64_t k = 0; k < N; ++k) {
+        mn = std::min(mn, std::min((double)m->pos1[k], (double)m->pos2[k]));
+        mx = std::max(mx, std::max((double)m->pos1[k], (double)m->pos2[k]));
+    }
+    std::vector<int32_t> b1(N), b2(N), db(N);
+    {
+        const EvenBins eb(mn, mx, (unsigned)n);
+        par_for(N, [&](int64_t lo, int64_t hi) {
+            for (int64_t k = lo; k < hi; ++k) { b1[k] = eb.bin((double)m->pos1[k]); b2[k] = eb.bin((double)m->pos2[k]); }
+        });
+        const int n1 = drop_unused(b1, (unsigned)n), n2 = drop_unused(b2, (unsigned)n);
+        if (n1 != n2) throw ArgError("bias binner: pos1 and pos2 do not populate the same bins");
+        nb_bias_ = n1;
+    }
+    // decay: K * bins_per_bf even bins of log(distance); support = mean log-distance per bin (ascending cell order)
+    std::vector<double> ld(N);
+    for (int64_t k = 0; k < N; ++k) {
+        if (!(m->distance[k] > 0)) throw ArgError("distance must be positive");
+        ld[k] = std::log(m->distance[k]);
+    }
+    dec_smin_ = *std::min_element(ld.begin(), ld.end()); dec_smax_ = *std::max_element(ld.begin(), ld.end());
+    {
+        const EvenBins eb(dec_smin_, dec_smax_, (unsigned)(kDecayK * kDecayBinsPerBf));
+        par_for(N, [&](int64_t lo, int64_t hi) { for (int64_t k = lo; k < hi; ++k) db[k] = eb.bin(ld[k]); });
+        nb_dec_ = drop_unused(db, (unsigned)(kDecayK * kDecayBinsPerBf));
+    }
+    std::vector<double> num(nb_dec_, 0.0), cnt(nb_dec_, 0.0);
+    for (int64_t k = 0; k < N; ++k) { num[db[k]] += ld[k]; cnt[db[k]] += 1.0; }
+    dec_support_.resize(nb_dec_);
+    for (int b = 0; b < nb_dec_; ++b) dec_support_[b] = num[b] / cnt[b];
+    // cell lists per bin
+    std::vector<int64_t> boff(nb_bias_ + 1, 0), doff(nb_dec_ + 1, 0);
+    for (int64_t k = 0; k < N; ++k) { boff[b1[k] + 1] += 1; if (b2[k] != b1[k]) boff[b2[k] + 1] += 1; doff[db[k] + 1] += 1; }
+    for (int b = 0; b < nb_bias_; ++b) boff[b + 1] += boff[b];
+    for (int b = 0; b < nb_dec_; ++b) doff[b + 1] += doff[b];
+    std::vector<uint32_t> blist(boff[nb_bias_]), dlist(doff[nb_dec_]);
+    {
+        std::vector<int64_t> bp(boff.begin(), boff.end() - 1), dp(doff.begin(), doff.end() - 1);
+        for (int64_t k = 0; k < N; ++k) {
+            if (b1[k] == b2[k]) blist[bp[b1[k]]++] = (uint32_t)k | 0x80000000u;
+            else { blist[bp[b1[k]]++] = (uint32_t)k; blist[bp[b2[k]]++] = (uint32_t)k; }
+            dlist[dp[db[k]]++] = (uint32_t)k;
+        }
+    }
+    cb1_.alloc(N); cb2_.alloc(N); cdb_.alloc(N);
+    bias_off_.alloc(boff.size()); dec_off_.alloc(doff.size());
+    bias_list_.alloc(std::max<size_t>(1, blist.size())); dec_list_.alloc(std::max<size_t>(1, dlist.size()));
+    cell_a_.alloc(N); cell_b_.alloc(N);
+    FB_CUDA(cudaMemcpy(cb1_.p, b1.data(), N * sizeof(int32_t), cudaMemcpyHostToDevice));
+    FB_CUDA(cudaMemcpy(cb2_.p, b2.data(), N * sizeof(int32_t), cudaMemcpyHostToDevice));
+    FB_CUDA(cudaMemcpy(cdb_.p, db.data(), N * sizeof(int32_t), cudaMemcpyHostToDevice));
+    FB_CUDA(cudaMemcpy(bias_off_.p, boff.data(), boff.size() * sizeof(int64_t), cudaMemcpyHostToDevice));
+    FB_CUDA(cudaMemcpy(dec_off_.p, doff.data(), doff.size() * sizeof(int64_t), cudaMemcpyHostToDevice));
+    FB_CUDA(cudaMemcpy(bias_list_.p, blist.data(), blist.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+    FB_CUDA(cudaMemcpy(dec_list_.p, dlist.data(), dlist.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+    tab_b_ = nb_bias_; tab_d_ = nb_dec_;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -246,6 +342,20 @@ void Model::ingest(int nbins, const fb_mat *m) {
 // ---------------------------------------------------------------------------------------------
 void Model::build_legs(double tol_val, unsigned free_decay) {
     const int n = t_.n, D = t_.D;
+    if (generic_) {   // the binners were evaluated cell by cell at ingest
+        dec_.setup(dec_support_, dec_smin_, dec_smax_, tol_val, free_decay);
+        std::vector<double> dummy;
+        std::fill(tab_h_.p, tab_h_.p + tab_h_.n, 0.0);
+        FB_CUDA(cudaMemcpyAsync(tab_.p, tab_h_.p, tab_h_.n * sizeof(double), cudaMemcpyHostToDevice, st_));
+        leg_sums(LEG_EXPO, MODE_NOBS, expo_nobs_, dummy);
+        leg_sums(LEG_DECAY, MODE_NOBS, dec_nobs_, dummy);
+        leg_sums(LEG_BIAS, MODE_NOBS, bias_nobs_, dummy);
+        for (auto &v : bias_nobs_) v = v / 2.; // fast_bias_mean.hpp:58
+        expo_est_.assign(D, 0.0);
+        bias_est_.assign(nb_bias_, 0.0);
+        legs_built_ = true;
+        return;
+    }
     // bias binner (fast_bias_mean.hpp:37-68): even bins between min and max position
     {
         const double mn = *std::min_element(pos_.begin(), pos_.end()), mx = *std::max_element(pos_.begin(), pos_.end());
@@ -281,14 +391,30 @@ void Model::upload_tables() {
     const int n = t_.n, D = t_.D;
     const std::vector<double> dc = dec_.binned_estimate();
     double *h = tab_h_.p;
-    for (int r = 0; r < n; ++r) h[r] = bias_est_[rowbin_[r]];       // Params<Mean>::mean stays 0
-    for (int k = 0; k < n; ++k) h[n + k] = dc[dbin_[k]];
-    for (int d = 0; d < D; ++d) h[2 * (size_t)n + d] = expo_est_[d];
+    if (generic_) {
+        for (int b = 0; b < nb_bias_; ++b) h[b] = bias_est_[b];
+        for (int k = 0; k < nb_dec_; ++k) h[tab_b_ + k] = dc[k];
+    } else {
+        for (int r = 0; r < n; ++r) h[r] = bias_est_[rowbin_[r]];       // Params<Mean>::mean stays 0
+        for (int k = 0; k < n; ++k) h[n + k] = dc[dbin_[k]];
+    }
+    for (int d = 0; d < D; ++d) h[(size_t)tab_b_ + tab_d_ + d] = expo_est_[d];
     FB_CUDA(cudaMemcpyAsync(tab_.p, h, tab_h_.n * sizeof(double), cudaMemcpyHostToDevice, st_));
     FB_CUDA(cudaStreamSynchronize(st_)); // tab_h_ is reused by the next fit
 }
 
 void Model::leg_sums(int leg, int mode, std::vector<double> &a, std::vector<double> &b) {
+    if (generic_ && leg != LEG_EXPO) {
+        const int nb = leg == LEG_BIAS ? nb_bias_ : nb_dec_;
+        leg_pass_cells(mode, t_, tables(tab_), alpha_, obs_.p, nobs_.p, phi_.p, nb, leg == LEG_BIAS ? bias_off_.p : dec_off_.p,
+                       leg == LEG_BIAS ? bias_list_.p : dec_list_.p, cell_a_.p, cell_b_.p, items_.p, st_);
+        kernel_launches += 2;
+        FB_CUDA(cudaMemcpyAsync(items_h_.p, items_.p, 2 * (size_t)nb * sizeof(double), cudaMemcpyDeviceToHost, st_));
+        FB_CUDA(cudaStreamSynchronize(st_));
+        a.resize(nb); b.resize(nb);
+        for (int k = 0; k < nb; ++k) { a[k] = items_h_.p[2 * k]; b[k] = items_h_.p[2 * k + 1]; }
+        return;
+    }
     leg_pass(leg, mode, t_, tables(tab_), alpha_, obs_.p, nobs_.p, phi_.p, part_.p, items_.p, st_);
     kernel_launches += 2;
     const int nitems = leg == LEG_EXPO ? t_.D : t_.n;
@@ -746,6 +872,62 @@ void Model::sweep_lambda(const fb_params *p, int nlam, const double *lam2v, fb_s
             if (out->steps) out->steps[o] = steps;
             if (out->bic) out->bic[o] = chisq + std::log(expo_nobs_[d]) * dof; // ScoreAssembler<BIC>: lsnc = log(sum nobs)
         }
+    }
+    kernel_launches += flo.kernel_launches;
+    out->ms_solver = ms_solver; out->admm_cell_iters = cell_iters;
+}
+
+// ---------------------------------------------------------------------------------------------
+// checkerboard cross-validation score (fastbinless.h: fb_cv_score)
+// ---------------------------------------------------------------------------------------------
+void Model::cv_score(const fb_params *p, int nlam, const double *lam2v, fb_cv_score_out *out) {
+    if (!p || !out || !lam2v || nlam < 0) throw ArgError("null argument");
+    if (!has_state_) throw StateError("cv_score needs a fitted or restored model");
+    const int n = t_.n, D = t_.D;
+    const int64_t nc = t_.ncells, N = t_.N();
+    alpha_ = p->alpha;
+    kernel_launches = 0;
+    const std::vector<double> lam1 = broadcast(p->lam1, p->n_lam1, D);
+    DevBuf<double> y(N), w(N), ycv(N), wcv(N), beta(nc), partial(2 * CV_BLOCKS), res(4);
+    PinBuf<double> res_h; res_h.alloc(4);
+    signal_yw(t_, tables(tab_), alpha_, obs_.p, nobs_.p, phi_.p, 0, y.p, w.p, st_);
+    kernel_launches += 1;
+    GflSolver flo(n, p->maxdiag, st_);
+    double ms_solver = 0;
+    int64_t cell_iters = 0;
+    std::vector<int> steps((size_t)std::max(1, nlam) * D * 2, 0);
+    std::vector<double> sums((size_t)std::max(1, nlam) * D * 4, 0.0);
+    for (int g = 0; g < 2; ++g) {      // group-major: the held-out (y, w) of a group is built once
+        signal_yw(t_, tables(tab_), alpha_, obs_.p, nobs_.p, phi_.p, (unsigned)(g + 1), ycv.p, wcv.p, st_);
+        kernel_launches += 1;
+        for (int k = 0; k < nlam; ++k) {
+            check_interrupt();
+            for (int d = 0; d < D; ++d) {
+                flo.reset();               // cold start (ScorePreparator.ipp:36-37)
+                const int st = flo.optimize(ycv.p + (size_t)d * nc, wcv.p + (size_t)d * nc, lam2v[k], p->tol_val / 20.);
+                ms_solver += flo.ms_last;
+                cell_iters += (int64_t)(st - 1) * flo.grid().ncells;
+                flo.get_beta_full(beta.p);
+                center_dataset(nc, nobs_.p + (size_t)d * nc, beta.p, scratch_.p + 16, st_);
+                cv_group_sum(n, g, y.p + (size_t)d * nc, w.p + (size_t)d * nc, beta.p, lam1[d], partial.p, res.p, st_);
+                kernel_launches += 1 + 3 + 2;
+                FB_CUDA(cudaMemcpyAsync(res_h.p, res.p, 2 * sizeof(double), cudaMemcpyDeviceToHost, st_));
+                FB_CUDA(cudaStreamSynchronize(st_));
+                const size_t o = (size_t)k * D + d;
+                steps[2 * o + g] = st;
+                sums[4 * o + 2 * g] = res_h.p[0]; sums[4 * o + 2 * g + 1] = res_h.p[1];
+            }
+        }
+    }
+    for (size_t o = 0; o < (size_t)nlam * D; ++o) {   // ScoreAssembler<CVkSD>::assemble (ScoreAssembler.hpp:24-36)
+        const double N0 = sums[4 * o + 1], N1 = sums[4 * o + 3];
+        const double cv0 = sums[4 * o] / N0, cv1 = sums[4 * o + 2] / N1;
+        const double Nt = N0 + N1;
+        const double cv = (N0 * cv0 + N1 * cv1) / Nt;
+        const double sd = std::sqrt((N0 * (cv0 - cv) * (cv0 - cv) + N1 * (cv1 - cv) * (cv1 - cv)) / (Nt - 1));
+        if (out->cv) out->cv[o] = cv;
+        if (out->cv_sd) out->cv_sd[o] = sd;
+        if (out->steps) { out->steps[2 * o] = steps[2 * o]; out->steps[2 * o + 1] = steps[2 * o + 1]; }
     }
     kernel_launches += flo.kernel_launches;
     out->ms_solver = ms_solver; out->admm_cell_iters = cell_iters;

@@ -46,6 +46,7 @@ public:
     void run_difference(int ref, const fb_params *p, fb_diff_out *out);
     void eval_cv(const fb_params *p, int nlam, const double *lam2, unsigned group, fb_cv_out *outs);
     void sweep_lambda(const fb_params *p, int nlam, const double *lam2, fb_sweep_out *out);
+    void cv_score(const fb_params *p, int nlam, const double *lam2, fb_cv_score_out *out);
 
     std::string err;
     int (*interrupt_cb)(void *) = nullptr;
@@ -76,7 +77,27 @@ private:
     DevBuf<double> part_, items_, scratch_;
     DevBuf<long long> keys_;
 
-    LegTables tables(const DevBuf<double> &b) const { return LegTables{b.p, b.p + t_.n, b.p + 2 * (size_t)t_.n}; }
+    // per-cell fallback (util.cpp:56-111 bins every cell): set by ingest when pos / distance are not
+    // functions of the bin / diagonal. Per cell the int32 bins of pos1, pos2 and log(distance); per leg bin the list of
+    // its cells (CSR; bit 31 of an entry = the cell counts twice); the tables are then indexed by leg bin.
+    bool generic_ = false;
+    DevBuf<int32_t> cb1_, cb2_, cdb_;
+    DevBuf<int64_t> bias_off_, dec_off_;
+    DevBuf<uint32_t> bias_list_, dec_list_;
+    DevBuf<double> cell_a_, cell_b_;
+    std::vector<double> dec_support_;
+    double dec_smin_ = 0, dec_smax_ = 0;
+    int tab_b_ = 0, tab_d_ = 0;                       // entries of the bias / decay part of the device tables
+
+    LegTables tables(const DevBuf<double> &b) const {
+        LegTables L{b.p, b.p + tab_b_, b.p + (size_t)tab_b_ + tab_d_};
+        if (generic_) { L.cb1 = cb1_.p; L.cb2 = cb2_.p; L.cdb = cdb_.p; }
+        return L;
+    }
+    void open_stream();
+    void close_stream();
+    void ingest_cells(const fb_mat *mat);
+    void alloc_tables();
     void ingest(int nbins, const fb_mat *mat);
     void ingest_reads(const fb_reads *reads, int *nbins_out);
     void alloc_work();
@@ -94,6 +115,6 @@ private:
     void upload_bytes(void *d_dst, const void *h_src, size_t bytes);
 };
 
-extern std::string g_last_error;
+extern thread_local std::string g_last_error;
 
 } // namespace fb

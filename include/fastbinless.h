@@ -197,6 +197,27 @@ typedef struct {
 } fb_sweep_out;
 FB_API int FB_NAME(sweep_lambda)(fb_handle *h, const fb_params *p, int nlam, const double *lam2, fb_sweep_out *out);
 
+/* Checkerboard cross-validation score of lambda2 values on a fitted or restored model: what a
+ * lambda2 search minimises. Per lambda2 value and dataset, for each of the two groups g = (bin1 + bin2) % 2 a COLD-START
+ * solve with the cells of the group held out (y = -100, w = 0: fast_binless.ipp:14-22; ScorePreparator.ipp:20-49), the
+ * solution centred like step_signal (fast_binless.ipp:33-44) and read at the held-out cells; then
+ *   chisq_i = w_i (phihat_i - soft(beta_cv_i, lam1))^2 + lam1^2        Likelihoods.hpp:25-42 (eCprime = 0), w / phihat not held out
+ *   CV_g = sum_{i in g} chisq_i / N_g,  CV = sum_g N_g CV_g / N,  CV_sd = sqrt(sum_g N_g (CV_g - CV)^2 / (N - 1))
+ *                                                                      ScoreAssembler.hpp:15-39
+ * cv / cv_sd hold nlam * ndatasets entries (lambda-major), steps 2 per entry (group 0, group 1); any pointer may be NULL. */
+typedef struct {
+    double *cv, *cv_sd;
+    int32_t *steps;
+    double ms_solver;
+    int64_t admm_cell_iters;
+} fb_cv_score_out;
+FB_API int FB_NAME(cv_score)(fb_handle *h, const fb_params *p, int nlam, const double *lam2, fb_cv_score_out *out);
+
+/* The csvfile writer of the reference (csvfile.hpp:30-117) for caller-owned columns: `header` (already quoted), then
+ * nrows rows of ncols values printed with 4 decimals. gzip != 0: one gzip member, what the reference as built writes
+ * (USE_BOOST = 1, binless/src/Makevars:1-2); 0: plain text (USE_BOOST = 0). Host only, no device needed. */
+FB_API int FB_NAME(csv_write)(const char *path, const char *header, int64_t nrows, int ncols, const double *const *cols, int gzip);
+
 /* Stand-alone fused-lasso solve on the triangle grid (the
  * FusedLassoGaussianEstimator<GFLLibrary> object of the reference,
  * FusedLassoGaussianEstimator.hpp:16-71, GFLLibraryTriangleImpl.cpp:60-71).

@@ -1207,6 +1207,65 @@ void sweep_lambda(Model &m, const fb_params *p, int nlam, const double *lam2v, f
     out->ms_solver = ms; out->admm_cell_iters = cell_iters;
 }
 
+/* checkerboard CV score (fastbinless.h: cv_score): ScorePreparator<CVkSD>::compute (ScorePreparator.ipp:20-49) with the
+ * fast path's hold-out convention (fast_binless.ipp:14-22) and centring (:33-44), chi square of Likelihoods.hpp:25-42
+ * (eCprime = 0), assembly of ScoreAssembler.hpp:24-36 */
+void cv_score(Model &m, const fb_params *p, int nlam, const double *lam2v, fb_cv_score_out *out) {
+    Data &d = m.d;
+    if (!m.has_state) throw std::logic_error("cv_score needs a fitted or restored model");
+    m.alpha = p->alpha;
+    const vec lam1 = broadcast(p->lam1, p->n_lam1, d.ndatasets);
+    vec res, wts;
+    m.residuals(d.beta, res, wts);
+    vec phihat(d.N);
+    for (unsigned i = 0; i < d.N; ++i) phihat[i] = res[i] + d.beta[i];
+    double ms = 0; int64_t cell_iters = 0;
+    const int ngroups = 2;
+    for (int k = 0; k < nlam; ++k)
+        for (unsigned ds = 0; ds < d.ndatasets; ++ds) {
+            const size_t off = (size_t)ds * d.ncells;
+            vec y(phihat.begin() + off, phihat.begin() + off + d.ncells), w(wts.begin() + off, wts.begin() + off + d.ncells);
+            ivec cvgroup(d.ncells);
+            for (unsigned i = 0; i < d.ncells; ++i) cvgroup[i] = (d.bin2[off + i] + d.bin1[off + i]) % ngroups;
+            vec beta_cv(d.ncells, 0.0);
+            const size_t o = (size_t)k * d.ndatasets + ds;
+            for (int g = 0; g < ngroups; ++g) {
+                vec y_cv(y), w_cv(w);
+                for (unsigned i = 0; i < d.ncells; ++i) if (cvgroup[i] == g) { y_cv[i] = -100; w_cv[i] = 0; }
+                GflSolver flo(d.nbins, p->maxdiag);   /* cold start */
+                double t0 = now_ms();
+                flo.optimize(y_cv, w_cv, lam2v[k], p->tol_val / 20.);
+                ms += now_ms() - t0;
+                cell_iters += (int64_t)(flo.last_steps - 1) * flo.N;
+                if (out->steps) out->steps[2 * o + g] = flo.last_steps;
+                vec values = flo.get();
+                double avg = 0, wsum = 0;
+                for (unsigned i = 0; i < d.ncells; ++i) { int no = d.nobs[off + i]; avg += values[i] * no; wsum += no; }
+                avg = avg / wsum;
+                for (unsigned i = 0; i < d.ncells; ++i) if (cvgroup[i] == g) beta_cv[i] = values[i] - avg;
+            }
+            vec chisq(d.ncells);
+            const double l1 = lam1[ds];
+            for (unsigned i = 0; i < d.ncells; ++i) {
+                const double b = beta_cv[i];
+                const double soft = (b > 0) ? std::max(0., b - l1) : std::min(0., b + l1);
+                chisq[i] = w[i] * (y[i] - soft) * (y[i] - soft) + l1 * l1;
+            }
+            vec gw, gcv;
+            for (int g = 0; g < ngroups; ++g) {
+                double Ni = 0, sum = 0;
+                for (unsigned i = 0; i < d.ncells; ++i) if (cvgroup[i] == g) { Ni += 1; sum += chisq[i]; }
+                gw.push_back(Ni); gcv.push_back(sum / Ni);
+            }
+            const double Nt = gw[0] + gw[1];
+            const double CV = (gw[0] * gcv[0] + gw[1] * gcv[1]) / Nt;
+            const double CV_sd = std::sqrt((gw[0] * (gcv[0] - CV) * (gcv[0] - CV) + gw[1] * (gcv[1] - CV) * (gcv[1] - CV)) / (Nt - 1));
+            if (out->cv) out->cv[o] = CV;
+            if (out->cv_sd) out->cv_sd[o] = CV_sd;
+        }
+    out->ms_solver = ms; out->admm_cell_iters = cell_iters;
+}
+
 } // namespace
 
 struct fb_handle { Model m; };
@@ -1311,6 +1370,19 @@ FB_API int fbo_eval_cv(fb_handle *h, const fb_params *p, int nlam, const double 
 }
 FB_API int fbo_sweep_lambda(fb_handle *h, const fb_params *p, int nlam, const double *lam2, fb_sweep_out *out) {
     ORACLE_TRY(h, sweep_lambda(h->m, p, nlam, lam2, out))
+}
+FB_API int fbo_cv_score(fb_handle *h, const fb_params *p, int nlam, const double *lam2, fb_cv_score_out *out) {
+    ORACLE_TRY(h, cv_score(h->m, p, nlam, lam2, out))
+}
+/* csvfile.hpp:30-117 row by row, plain text (the oracle does not link zlib: tests gunzip the product's file and compare) */
+FB_API int fbo_csv_write(const char *path, const char *header, int64_t nrows, int ncols, const double *const *cols, int) {
+    FILE *f = std::fopen(path, "w");
+    if (!f) return 1;
+    std::fprintf(f, "%s\n", header);
+    for (int64_t i = 0; i < nrows; ++i)
+        for (int c = 0; c < ncols; ++c) std::fprintf(f, c + 1 == ncols ? "%.4f\n" : "%.4f,", cols[c][i]);
+    std::fclose(f);
+    return FB_OK;
 }
 FB_API int64_t fbo_kernel_launches(const fb_handle *) { return 0; }
 FB_API void fbo_release_cached_memory(void) {}

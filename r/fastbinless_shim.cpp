@@ -25,13 +25,15 @@ struct HandleGuard {
 };
 
 void check(int rc, const fb_handle *h) {
+    // the callback below saw a pending user interrupt: raise it as the interrupt it is (the reference's
+    // Rcpp::checkUserInterrupt() in the outer loop, fast_binless.cpp:124), not as an error
+    if (rc == FB_ERR_INTERRUPT) throw Rcpp::internal::InterruptedException();
     if (rc != FB_OK) Rcpp::stop(std::string(fb_last_error(h)));   // same channel as the reference's Rcpp::stop
 }
 
-int interrupt_cb(void *) {                                       // Rcpp::checkUserInterrupt() once per outer step
-    try { Rcpp::checkUserInterrupt(); } catch (...) { return 1; }
-    return 0;
-}
+// asks R whether an interrupt is pending WITHOUT unwinding through the library's frames (R_CheckUserInterrupt would longjmp)
+void check_interrupt_fn(void *) { R_CheckUserInterrupt(); }
+int interrupt_cb(void *) { return R_ToplevelExec(check_interrupt_fn, nullptr) == FALSE ? 1 : 0; }
 
 // FastDataCore's view of the data frame (FastData.ipp:5-14): factors arrive as their integer codes
 fb_mat as_fb_mat(const DataFrame &obs, IntegerVector &name, IntegerVector &bin1, IntegerVector &pos1,
@@ -73,26 +75,38 @@ List fast_binless_cuda(const DataFrame obs, unsigned nbins, double alpha, const 
     fb_set_interrupt_cb(g.h, interrupt_cb, nullptr);
     const R_xlen_t N = m.N;
     const int D = Rcpp::max(name);
-    NumericVector background(N), biasmat(N), decaymat(N), signal(N), binless(N), phihat(N), weight(N), log_signal(N);
-    IntegerVector patchno(N);
+    // csv_out: the reference streams the seven computed columns to the (gzip) file and returns mat = 1
+    // (fast_dataframe.cpp:23-57); the library then needs no host columns at all, only log_signal for the list
+    const bool csv = !csv_out.empty();
+    const R_xlen_t Nc = csv ? 0 : N;
+    NumericVector background(Nc), biasmat(Nc), decaymat(Nc), signal(Nc), binless(Nc), phihat(Nc), weight(Nc), log_signal(N);
+    IntegerVector patchno(Nc);
     NumericVector bias_est(nbins), expo_est(D);
     fb_signal_out o = fb_signal_out();
-    o.background = background.begin(); o.biasmat = biasmat.begin(); o.decaymat = decaymat.begin();
-    o.signal = signal.begin(); o.binless = binless.begin(); o.phihat = phihat.begin(); o.weight = weight.begin();
-    o.patchno = patchno.begin(); o.log_signal = log_signal.begin();
+    if (!csv) {
+        o.background = background.begin(); o.biasmat = biasmat.begin(); o.decaymat = decaymat.begin();
+        o.signal = signal.begin(); o.binless = binless.begin(); o.phihat = phihat.begin(); o.weight = weight.begin();
+        o.patchno = patchno.begin();
+    }
+    o.log_signal = log_signal.begin();
     o.biases.estimate = bias_est.begin(); o.exposures.estimate = expo_est.begin();
     fb_params p = as_fb_params(alpha, lam2, lam1, nouter, tol_val, bg_steps, free_decay, compute_patchnos, csv_out, maxdiag);
     check(fb_run_signal(g.h, &p, &o), g.h);
-    // the reference returns name/bin1/bin2 as the ordered factors it was given (FastData.hpp:27-29,50-55): pass them through
-    DataFrame mat = DataFrame::create(_["name"] = obs["name"], _["bin1"] = obs["bin1"], _["pos1"] = pos1,
-                                      _["bin2"] = obs["bin2"], _["pos2"] = pos2, _["observed"] = observed,
-                                      _["nobs"] = nobs, _["distance"] = distance, _["background"] = background,
-                                      _["biasmat"] = biasmat, _["decaymat"] = decaymat, _["signal"] = signal,
-                                      _["binless"] = binless, _["phihat"] = phihat, _["weight"] = weight,
-                                      _["patchno"] = NumericVector(patchno.begin(), patchno.end()));
+    SEXP mat_sexp;
+    if (csv) mat_sexp = Rcpp::wrap(1);
+    else {
+        // the reference returns name/bin1/bin2 as the ordered factors it was given (FastData.hpp:27-29,50-55): pass them through
+        DataFrame mat = DataFrame::create(_["name"] = obs["name"], _["bin1"] = obs["bin1"], _["pos1"] = pos1,
+                                          _["bin2"] = obs["bin2"], _["pos2"] = pos2, _["observed"] = observed,
+                                          _["nobs"] = nobs, _["distance"] = distance, _["background"] = background,
+                                          _["biasmat"] = biasmat, _["decaymat"] = decaymat, _["signal"] = signal,
+                                          _["binless"] = binless, _["phihat"] = phihat, _["weight"] = weight,
+                                          _["patchno"] = NumericVector(patchno.begin(), patchno.end()));
+        mat_sexp = mat;
+    }
     NumericVector beta(o.decay.beta, o.decay.beta + FB_DECAY_K);
     if (o.biases.n < (int)nbins) bias_est = NumericVector(bias_est.begin(), bias_est.begin() + o.biases.n);
-    return List::create(_["mat"] = mat,
+    return List::create(_["mat"] = mat_sexp,
                         _["biases"] = List::create(_["estimate"] = bias_est, _["mean"] = o.biases.mean),
                         _["decay"] = List::create(_["beta"] = beta, _["lambda"] = o.decay.lambda, _["mean"] = o.decay.mean),
                         _["exposures"] = List::create(_["estimate"] = expo_est, _["mean"] = o.exposures.mean),

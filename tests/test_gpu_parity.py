@@ -190,7 +190,10 @@ def test_input_errors(gpu_lib):
     with pytest.raises(FastBinlessError, match="sorted"):
         gpu_lib.create(bad, 10)
     bad = dict(mat); bad["distance"] = mat["distance"].copy(); bad["distance"][3] += 1
-    with pytest.raises(FastBinlessError, match="bin_data layout"):
+    with gpu_lib.create(bad, 10) as h:      # not a bin_data() layout: accepted, binned per cell
+        assert h.run_signal(0.5, 2.5)["diagnostics"]["nsteps"] >= 1
+    bad = dict(mat); bad["distance"] = mat["distance"].copy(); bad["distance"][3] = 0.0
+    with pytest.raises(FastBinlessError, match="distance must be positive"):
         gpu_lib.create(bad, 10)
     with gpu_lib.create(mat, 10) as h:
         with pytest.raises(FastBinlessError) as ei:
@@ -302,15 +305,18 @@ def test_sweep_lambda_matches_oracle(gpu_lib, oracle):
 
 
 def test_csv_out_matches_oracle(gpu_lib, oracle, tmp_path):
-    """csv_out (fast_dataframe.cpp:23-57, csvfile.hpp with USE_BOOST = 0): quoted header + one "%.4f" row per cell."""
+    """csv_out (fast_dataframe.cpp:23-57): the reference as built streams gzip (csvfile.hpp:46-48, USE_BOOST = 1 in
+    binless/src/Makevars:1-2): quoted header + one "%.4f" row per cell; gunzip of the product's file = the oracle's text."""
+    import gzip
     n, D = 33, 2
     mat = synth(n, D, 5000, 3)
-    fg, fo = str(tmp_path / "gpu.csv"), str(tmp_path / "cpu.csv")
+    fg, fo = str(tmp_path / "gpu.csv.gz"), str(tmp_path / "cpu.csv")
     with gpu_lib.create(mat, n) as hg:
         hg.run_signal(0.49, [2.53, 4.51], [0.13, 0.10], csv_out=fg)
     with oracle.create(mat, n) as ho:
         ho.run_signal(0.49, [2.53, 4.51], [0.13, 0.10], csv_out=fo)
-    lg, lo = open(fg).read().splitlines(), open(fo).read().splitlines()
+    assert open(fg, "rb").read(3) == b"\x1f\x8b\x08"
+    lg, lo = gzip.open(fg, "rt").read().splitlines(), open(fo).read().splitlines()
     assert lg[0] == lo[0] == '"phihat","weight","biasmat","decaymat","signal","binless","background"'
     assert len(lg) == len(lo) == 1 + D * n * (n + 1) // 2
     a = np.array([[float(x) for x in l.split(",")] for l in lg[1:]])
@@ -318,6 +324,67 @@ def test_csv_out_matches_oracle(gpu_lib, oracle, tmp_path):
     assert np.abs(a - b).max() <= 1.0001e-4            # 4 printed decimals: at most one unit in the last place
     assert np.mean(np.array(lg[1:]) == np.array(lo[1:])) > 0.999
     assert all(len(l.split(",")) == 7 and all(len(x.split(".")[1]) == 4 for x in l.split(",")) for l in lg[1:50])
+
+
+def test_cv_score_matches_oracle(gpu_lib, oracle):
+    """fb_cv_score (ScoreAssembler.hpp:15-39 on checkerboard hold-out solves) against the oracle:
+    same ADMM step counts of every held-out solve, CV and CV_sd to 1e-9 relative."""
+    n, D = 40, 2
+    mat = synth(n, D, 5000, 8)
+    lams = [0.8, 2.5, 7.0]
+    with oracle.create(mat, n) as ho:
+        fit = ho.run_signal(0.5, 2.5, 0.0)
+        ro = ho.cv_score(0.5, lams, [0.05, 0.0], tol_val=0.2)
+    with gpu_lib.create(mat, n) as hg:
+        hg.restore(fit["log_signal"], fit["biases"], fit["decay"], fit["exposures"])
+        rg = hg.cv_score(0.5, lams, [0.05, 0.0], tol_val=0.2)
+        assert hg.kernel_launches() > 0
+    assert np.array_equal(rg["steps"], ro["steps"])
+    assert np.allclose(rg["cv"], ro["cv"], rtol=1e-9, atol=0)
+    assert np.allclose(rg["cv_sd"], ro["cv_sd"], rtol=1e-7, atol=1e-12)
+    assert rg["admm_cell_iters"] == ro["admm_cell_iters"]
+
+
+def _jittered(n, D, seed):
+    """a matrix that is NOT a bin_data() layout: distance varies inside a diagonal, positions differ between datasets"""
+    mat = synth(n, D, 5000, seed)
+    rng = np.random.default_rng(seed)
+    nc = n * (n + 1) // 2
+    mat = {k: np.array(v, copy=True) for k, v in mat.items()}
+    mat["distance"] = mat["distance"] * np.exp(rng.uniform(-0.02, 0.02, mat["distance"].size))
+    for d in range(1, D):
+        mat["pos1"][d * nc:(d + 1) * nc] += 7 * d
+        mat["pos2"][d * nc:(d + 1) * nc] += 7 * d
+    return mat
+
+
+@pytest.mark.parametrize("n,D,seed", [(33, 2, 3), (129, 1, 5), (200, 2, 1)])
+def test_per_cell_binner_fallback_matches_oracle(gpu_lib, oracle, n, D, seed):
+    """inputs whose pos / distance are not functions of the bin / diagonal are binned cell by cell
+    (util.cpp:56-111, fast_decay.hpp:48-68, fast_bias_mean.hpp:37-68) instead of being refused."""
+    mat = _jittered(n, D, seed)
+    with oracle.create(mat, n) as ho:
+        oo = ho.run_signal(0.49, 2.5, 0.1)
+        do = ho.run_difference(1, 0.49, 3.0, 0.1) if D > 1 else None
+    with gpu_lib.create(mat, n) as hg:
+        og = hg.run_signal(0.49, 2.5, 0.1)
+        dg = hg.run_difference(1, 0.49, 3.0, 0.1) if D > 1 else None
+    compare_signal(og, oo)
+    if D > 1:
+        compare_diff(dg, do)
+
+
+def test_per_cell_binner_equals_closed_form_on_bin_data_layout(gpu_lib, monkeypatch):
+    """FB_FORCE_CELL_BINS=1 sends a regular bin_data() matrix through the per-cell binner: same outer steps and ADMM
+    iteration counts, outputs equal up to the summation order of the leg sums."""
+    n, D = 96, 2
+    mat = synth(n, D, 5000, 21)
+    with gpu_lib.create(mat, n) as h:
+        a = h.run_signal(0.5, 2.5, 0.0)
+    monkeypatch.setenv("FB_FORCE_CELL_BINS", "1")
+    with gpu_lib.create(mat, n) as h:
+        b = h.run_signal(0.5, 2.5, 0.0)
+    compare_signal(b, a)
 
 
 def test_trail_block_sharding_on_two_gpus():
