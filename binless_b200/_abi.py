@@ -69,6 +69,36 @@ class fb_cv_score_out(C.Structure):
     _fields_ = [("cv", c_dp), ("cv_sd", c_dp), ("steps", c_ip), ("ms_solver", C.c_double), ("admm_cell_iters", C.c_int64)]
 
 
+class fb_cts(C.Structure):
+    _fields_ = [("N", C.c_int64), ("bin1", c_ip), ("bin2", c_ip), ("count", c_dp), ("lmu_nosig", c_dp), ("nobs", c_dp),
+                ("log_decay", c_dp)]
+
+
+class fb_perf_meta(C.Structure):
+    _fields_ = [("n_bad_rows", C.c_int), ("bad_rows", c_ip), ("n_bad_diags", C.c_int), ("bad_diags", c_ip), ("diag_grp", c_ip)]
+
+
+class fb_perf_params(C.Structure):
+    _fields_ = [("dispersion", C.c_double), ("nouter", C.c_int), ("lam2", C.c_double), ("tol_val", C.c_double),
+                ("constrained", C.c_int), ("fixed", C.c_int), ("positive", C.c_int), ("lambda1_fixed", C.c_int),
+                ("lambda1_fix_value", C.c_double)]
+
+
+class fb_perf_signal_out(C.Structure):
+    _fields_ = [("phi", c_dp), ("beta", c_dp), ("phihat", c_dp), ("nobs", c_dp), ("weight", c_dp), ("patchno", c_ip),
+                ("dof", C.c_int), ("converged", C.c_int), ("nouter_done", C.c_int), ("ncandidates", C.c_int),
+                ("BIC", C.c_double), ("BIC_sd", C.c_double), ("eCprime", C.c_double), ("lambda1", C.c_double),
+                ("admm_iters", C.c_int64)]
+
+
+class fb_perf_diff_out(C.Structure):
+    _fields_ = [("phi_ref", c_dp), ("delta", c_dp), ("beta", c_dp), ("phihat", c_dp), ("phihat_var", c_dp),
+                ("phihat_ref", c_dp), ("phihat_var_ref", c_dp), ("nobs", c_dp), ("deltahat", c_dp), ("weight", c_dp),
+                ("patchno", c_ip), ("dof", C.c_int), ("converged", C.c_int), ("nouter_done", C.c_int),
+                ("ncandidates", C.c_int), ("BIC", C.c_double), ("BIC_sd", C.c_double), ("lambda1", C.c_double),
+                ("admm_iters", C.c_int64)]
+
+
 class fb_gfl_state(C.Structure):
     _fields_ = [("beta", c_dp), ("z", c_dp), ("u", c_dp), ("alpha", C.c_double), ("steps", C.c_int)]
 
@@ -76,7 +106,8 @@ class fb_gfl_state(C.Structure):
 ENTRY_POINTS = ["create", "destroy", "last_error", "run_signal", "restore", "run_difference",
                 "eval_cv", "sweep_lambda", "gfl_solve", "set_interrupt_cb", "kernel_launches", "release_cached_memory",
                 "comm_unique_id", "comm_init", "comm_destroy", "comm_rank", "comm_world", "shard_plan",
-                "create_binned", "get_mat", "mat_rows", "cv_score", "csv_write"]
+                "create_binned", "get_mat", "mat_rows", "cv_score", "csv_write",
+                "wgfl_signal_bic", "wgfl_diff_bic"]
 
 
 def _dp(a):
@@ -148,6 +179,14 @@ class FastBinlessLib:
         self._csv_write = f("csv_write")
         self._csv_write.argtypes = [C.c_char_p, C.c_char_p, C.c_int64, C.c_int, C.POINTER(c_dp), C.c_int]
         self._csv_write.restype = C.c_int
+        self._wgfl_signal_bic = f("wgfl_signal_bic")
+        self._wgfl_signal_bic.argtypes = [C.c_int, C.POINTER(fb_cts), C.POINTER(fb_perf_meta), C.POINTER(fb_perf_params), c_dp,
+                                          C.c_int, C.POINTER(fb_gfl_state), C.POINTER(fb_perf_signal_out)]
+        self._wgfl_signal_bic.restype = C.c_int
+        self._wgfl_diff_bic = f("wgfl_diff_bic")
+        self._wgfl_diff_bic.argtypes = [C.c_int, C.POINTER(fb_cts), C.POINTER(fb_cts), C.POINTER(fb_perf_meta),
+                                        C.POINTER(fb_perf_params), c_dp, c_dp, C.c_int, C.POINTER(fb_gfl_state), C.POINTER(fb_perf_diff_out)]
+        self._wgfl_diff_bic.restype = C.c_int
         self._kernel_launches = f("kernel_launches")
         self._kernel_launches.argtypes = [C.c_void_p]; self._kernel_launches.restype = C.c_int64
         self._gfl_solve = f("gfl_solve")
@@ -377,6 +416,74 @@ def _cv_score_impl(self, alpha, lam2, lam1=0.0, tol_val=0.2, maxdiag=0):
 
 
 Handle.cv_score = _cv_score_impl
+
+
+def _cts_struct(cts, keep):
+    cols = {k: _i32(cts[k]) if k in ("bin1", "bin2") else _f64(cts[k]) for k in ("bin1", "bin2", "count", "lmu_nosig", "nobs", "log_decay")}
+    keep.append(cols)
+    return fb_cts(N=cols["bin1"].size, bin1=_ip(cols["bin1"]), bin2=_ip(cols["bin2"]), count=_dp(cols["count"]),
+                  lmu_nosig=_dp(cols["lmu_nosig"]), nobs=_dp(cols["nobs"]), log_decay=_dp(cols["log_decay"]))
+
+
+def _meta_struct(md, keep):
+    br = _i32(md.get("bad_rows", [])); bd = _i32(md.get("bad_diags", [])); dg = _i32(md["diag_grp"])
+    keep.append((br, bd, dg))
+    return fb_perf_meta(n_bad_rows=br.size, bad_rows=_ip(br), n_bad_diags=bd.size, bad_diags=_ip(bd), diag_grp=_ip(dg))
+
+
+def wgfl_signal_bic(lib: FastBinlessLib, cts, dispersion, nouter, nbins, gfl_state, lam2, tol_val, metadata, beta,
+                    constrained, fixed, positive=True, lambda1_fixed=False, lambda1_fix_value=0.0):
+    """wgfl_signal_BIC (perf_iteration_signal.cpp:22-157) through the C ABI; arguments in the reference's order."""
+    keep = []
+    nc = nbins * (nbins + 1) // 2
+    c = _cts_struct(cts, keep); m = _meta_struct(metadata, keep)
+    p = fb_perf_params(dispersion=float(dispersion), nouter=int(nouter), lam2=float(lam2), tol_val=float(tol_val),
+                       constrained=int(bool(constrained)), fixed=int(bool(fixed)), positive=int(bool(positive)),
+                       lambda1_fixed=int(bool(lambda1_fixed)), lambda1_fix_value=float(lambda1_fix_value))
+    b0 = _f64(beta)
+    sb, sz, su = (np.zeros(nc), np.zeros(2 * nc - 2), np.zeros(2 * nc - 2))
+    warm = bool(gfl_state)
+    if warm:
+        sb[:] = gfl_state["beta"]; sz[:] = gfl_state["z"]; su[:] = gfl_state["u"]
+    st = fb_gfl_state(beta=_dp(sb), z=_dp(sz), u=_dp(su), alpha=float(gfl_state["alpha"]) if warm else 5.0, steps=0)
+    cols = {k: np.empty(nc) for k in ("phi", "beta", "phihat", "nobs", "weight")}
+    patch = np.empty(nc, dtype=np.int32)
+    o = fb_perf_signal_out(patchno=_ip(patch), **{k: _dp(v) for k, v in cols.items()})
+    rc = lib._wgfl_signal_bic(int(nbins), C.byref(c), C.byref(m), C.byref(p), _dp(b0), int(warm), C.byref(st), C.byref(o))
+    lib._check(rc, None)
+    res = dict(cols); res["patchno"] = patch
+    res.update(dof=o.dof, converged=bool(o.converged), nouter_done=o.nouter_done, ncandidates=o.ncandidates, BIC=o.BIC,
+               BIC_sd=o.BIC_sd, eCprime=o.eCprime, lambda1=o.lambda1, lambda2=float(lam2), admm_iters=int(o.admm_iters),
+               GFLState={"beta": sb, "z": sz, "u": su, "alpha": st.alpha})
+    return res
+
+
+def wgfl_diff_bic(lib: FastBinlessLib, cts, ref, dispersion, nouter, nbins, gfl_state, lam2, tol_val, metadata, phi_ref,
+                  beta, constrained, lambda1_fixed=False, lambda1_fix_value=0.0):
+    """wgfl_diff_BIC (perf_iteration_diff.cpp:20-117) through the C ABI; arguments in the reference's order."""
+    keep = []
+    nc = nbins * (nbins + 1) // 2
+    c = _cts_struct(cts, keep); r = _cts_struct(ref, keep); m = _meta_struct(metadata, keep)
+    p = fb_perf_params(dispersion=float(dispersion), nouter=int(nouter), lam2=float(lam2), tol_val=float(tol_val),
+                       constrained=int(bool(constrained)), fixed=1, positive=0,
+                       lambda1_fixed=int(bool(lambda1_fixed)), lambda1_fix_value=float(lambda1_fix_value))
+    b0 = _f64(beta); pr0 = _f64(phi_ref)
+    sb, sz, su = (np.zeros(nc), np.zeros(2 * nc - 2), np.zeros(2 * nc - 2))
+    warm = bool(gfl_state)
+    if warm:
+        sb[:] = gfl_state["beta"]; sz[:] = gfl_state["z"]; su[:] = gfl_state["u"]
+    st = fb_gfl_state(beta=_dp(sb), z=_dp(sz), u=_dp(su), alpha=float(gfl_state["alpha"]) if warm else 5.0, steps=0)
+    names = ("phi_ref", "delta", "beta", "phihat", "phihat_var", "phihat_ref", "phihat_var_ref", "nobs", "deltahat", "weight")
+    cols = {k: np.empty(nc) for k in names}
+    patch = np.empty(nc, dtype=np.int32)
+    o = fb_perf_diff_out(patchno=_ip(patch), **{k: _dp(v) for k, v in cols.items()})
+    rc = lib._wgfl_diff_bic(int(nbins), C.byref(c), C.byref(r), C.byref(m), C.byref(p), _dp(pr0), _dp(b0), int(warm), C.byref(st), C.byref(o))
+    lib._check(rc, None)
+    res = dict(cols); res["patchno"] = patch
+    res.update(dof=o.dof, converged=bool(o.converged), nouter_done=o.nouter_done, ncandidates=o.ncandidates, BIC=o.BIC,
+               BIC_sd=o.BIC_sd, eCprime=0.0, lambda1=o.lambda1, lambda2=float(lam2), admm_iters=int(o.admm_iters),
+               GFLState={"beta": sb, "z": sz, "u": su, "alpha": st.alpha})
+    return res
 
 
 def gfl_solve(lib: FastBinlessLib, nbins, y, w, lam2, converge, maxsteps=30000, maxdiag=0, state=None):

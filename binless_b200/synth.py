@@ -13,7 +13,7 @@ from __future__ import annotations
 
 import numpy as np
 
-__all__ = ["synth", "synth_reads", "tri_indices", "CONFIGS"]
+__all__ = ["synth", "synth_reads", "synth_cts", "tri_indices", "CONFIGS"]
 
 # the named workloads of BASELINE.json / SURVEY.md section 8
 CONFIGS = {
@@ -138,3 +138,33 @@ def synth_reads(nbins: int, ndatasets: int, res: int = 5000, seed: int = 1, read
     out = {"cut_name": np.concatenate(cut_name).astype(np.int32), "cut_pos": np.concatenate(cut_pos).astype(np.int32)}
     out.update({k: np.concatenate(v).astype(np.int32) for k, v in rd.items()})
     return out
+
+
+def synth_cts(nbins: int, seed: int = 1, rows_per_cell: float = 2.5, dispersion: float = 2.0, shift: float = 0.0):
+    """The `cts` data frame and `metadata` list of the optimized path (what binless:::csnorm_predict_binned hands to
+    wgfl_signal_BIC, /root/reference/binless/src/perf_iteration_signal.cpp:22-30; columns read by cts_to_mat.cpp:43-50):
+    several rows per bin pair (one per cut-site category), 1-based bins, sorted by (bin1, bin2); a few cells have no row.
+    `shift` moves the planted signal so that a second call gives the `ref` / `cts` pair of wgfl_diff_BIC."""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    bi, bj = tri_indices(nbins)
+    k = rng.poisson(rows_per_cell, size=bi.size)
+    k[rng.random(bi.size) < 0.03] = 0
+    b1 = np.repeat(bi + 1, k).astype(np.int32); b2 = np.repeat(bj + 1, k).astype(np.int32)
+    n = b1.size
+    d = (b2 - b1).astype(np.float64)
+    log_decay = -0.9 * np.log1p(d) + rng.normal(0, 0.02, n)
+    tad = (np.arange(nbins) // max(4, nbins // 5))
+    phi_cell = np.where(tad[bi] == tad[bj], 0.8 + shift, 0.0)
+    a, b = nbins // 3, (2 * nbins) // 3
+    phi_cell = phi_cell + (1.2 - shift) * np.exp(-((bi - a) ** 2 + (bj - b) ** 2) / 6.0)
+    phi = np.repeat(phi_cell, k)
+    lmu_nosig = 1.0 + log_decay + rng.normal(0, 0.1, n)
+    nobs = rng.integers(1, 40, size=n).astype(np.float64)
+    mu = np.exp(lmu_nosig + phi)
+    lam = rng.gamma(shape=dispersion, scale=mu / dispersion)
+    count = rng.poisson(lam).astype(np.float64)
+    diag_grp = np.floor(np.log2(np.arange(nbins) + 1)).astype(np.int32)
+    return {"bin1": b1, "bin2": b2, "count": count, "lmu_nosig": lmu_nosig, "nobs": nobs, "log_decay": log_decay,
+            "metadata": {"bad_rows": np.array([max(1, nbins // 2)], dtype=np.int32),
+                         "bad_diags": np.array([nbins - 1], dtype=np.int32), "diag_grp": diag_grp},
+            "nbins": nbins, "dispersion": dispersion}

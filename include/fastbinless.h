@@ -235,6 +235,57 @@ FB_API int FB_NAME(gfl_solve)(int nbins, unsigned maxdiag, const double *y, cons
                               double lam2, double converge, int maxsteps, int warm,
                               fb_gfl_state *st, double *beta_full);
 
+/* ---- Optimized-path performance iteration on the same fused-lasso kernels ----
+ * wgfl_signal_BIC (perf_iteration_signal.cpp:22-157) and wgfl_diff_BIC (perf_iteration_diff.cpp:20-117) of the reference:
+ * the IRLS alternation of IRLSEstimator.hpp:28-60 between the scatter-add front end cts_to_signal_mat_core
+ * (cts_core.c:5-47, through cts_to_mat.cpp:14-124 with its outlier rows / diagonals) and the triangle-grid fused lasso
+ * (warm first, then a cold restart if it did not converge), the patch numbers of the result, and the lambda1 / eCprime
+ * choice by BIC: EstimatedSparsity.ipp:11-30 over the candidates of candidate_generation.cpp / minimum_UB.cpp /
+ * BoundsOptimizer.ipp, or FixedSparsity.hpp with BoundsRectifier.hpp; the likelihood is evaluated on a COLD-START
+ * re-solve at lambda2 (ScorePreparator.ipp:53-64, Likelihoods.hpp:25-95), the degrees of freedom on the warm solution
+ * (DOFComputer.hpp:16-24), BIC = sum chisq + log(sum nobs) dof (ScoreAssembler.hpp:41-55).
+ * `cts` is the reference's cts data frame: one row per (bin pair, cut-site category) with 1-based bins, bin2 >= bin1. */
+typedef struct {
+    int64_t N;
+    const int32_t *bin1, *bin2;
+    const double *count, *lmu_nosig, *nobs, *log_decay;
+} fb_cts;
+typedef struct {                        /* the `metadata` list (cts_to_mat.cpp:14-32,86-90) */
+    int n_bad_rows;  const int32_t *bad_rows;      /* bins (1-based) whose rows and columns are outliers */
+    int n_bad_diags; const int32_t *bad_diags;     /* outlier diagonals, as bin2 - bin1 */
+    const int32_t *diag_grp;                       /* nbins entries: group of diagonal bin2 - bin1 */
+} fb_perf_meta;
+typedef struct {
+    double dispersion; int nouter; double lam2, tol_val;
+    int constrained;                   /* ForbidDegeneracy / AllowDegeneracy */
+    int fixed, positive;               /* signal only: eCprime fixed at 0 (ZeroOffset) / PositiveSign; fixed == 0 implies positive */
+    int lambda1_fixed; double lambda1_fix_value;
+} fb_perf_params;
+/* Arrays have nbins(nbins+1)/2 entries; any may be NULL. `gfl` carries the GFLState list in (read when warm != 0; warm == 0
+ * is the empty list: cold start with alpha = 5) and out (the state after the IRLS iterations, before the BIC re-solve
+ * resets the solver; arrays that are NULL are not written). */
+typedef struct {
+    double *phi, *beta;                             /* soft-thresholded and raw solution */
+    double *phihat, *nobs, *weight;                 /* mat columns (cts_to_mat.cpp:92-99) */
+    int32_t *patchno;
+    int dof, converged, nouter_done, ncandidates;
+    double BIC, BIC_sd, eCprime, lambda1;
+    int64_t admm_iters;                             /* ADMM iterations over all solves of the call (diagnostic) */
+} fb_perf_signal_out;
+typedef struct {
+    double *phi_ref, *delta, *beta;
+    double *phihat, *phihat_var, *phihat_ref, *phihat_var_ref, *nobs, *deltahat, *weight;
+    int32_t *patchno;
+    int dof, converged, nouter_done, ncandidates;
+    double BIC, BIC_sd, lambda1;
+    int64_t admm_iters;
+} fb_perf_diff_out;
+FB_API int FB_NAME(wgfl_signal_bic)(int nbins, const fb_cts *cts, const fb_perf_meta *meta, const fb_perf_params *p,
+                                    const double *beta_init, int warm, fb_gfl_state *gfl, fb_perf_signal_out *out);
+FB_API int FB_NAME(wgfl_diff_bic)(int nbins, const fb_cts *cts, const fb_cts *ref, const fb_perf_meta *meta,
+                                  const fb_perf_params *p, const double *phi_ref_init, const double *beta_init,
+                                  int warm, fb_gfl_state *gfl, fb_perf_diff_out *out);
+
 /* Device and pinned-host blocks of destroyed handles are kept in a size-keyed cache (cudaMalloc / cudaFree cost
  * milliseconds per call and fast_binless is called once per locus); this returns them to the driver. */
 FB_API void FB_NAME(release_cached_memory)(void);

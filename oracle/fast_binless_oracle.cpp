@@ -35,6 +35,7 @@
 #include <cstring>
 #include <limits>
 #include <map>
+#include <set>
 #include <memory>
 #include <numeric>
 #include <stdexcept>
@@ -1268,6 +1269,8 @@ void cv_score(Model &m, const fb_params *p, int nlam, const double *lam2v, fb_cv
 
 } // namespace
 
+#include "perf_iteration_oracle.hpp"
+
 struct fb_handle { Model m; };
 
 #define ORACLE_TRY(h, body)                                                     \
@@ -1382,6 +1385,29 @@ FB_API int fbo_csv_write(const char *path, const char *header, int64_t nrows, in
     for (int64_t i = 0; i < nrows; ++i)
         for (int c = 0; c < ncols; ++c) std::fprintf(f, c + 1 == ncols ? "%.4f\n" : "%.4f,", cols[c][i]);
     std::fclose(f);
+    return FB_OK;
+}
+FB_API int fbo_wgfl_signal_bic(int nbins, const fb_cts *cts, const fb_perf_meta *meta, const fb_perf_params *p,
+                               const double *beta_init, int warm, fb_gfl_state *gfl, fb_perf_signal_out *out) {
+    try { perf_wgfl_signal(nbins, cts, meta, p, beta_init, warm, gfl, out); return FB_OK; }
+    catch (const std::exception &e) { g_create_error = e.what(); return FB_ERR_ARG; }
+}
+FB_API int fbo_wgfl_diff_bic(int nbins, const fb_cts *cts, const fb_cts *ref, const fb_perf_meta *meta, const fb_perf_params *p,
+                             const double *phi_ref_init, const double *beta_init, int warm, fb_gfl_state *gfl, fb_perf_diff_out *out) {
+    try { perf_wgfl_diff(nbins, cts, ref, meta, p, phi_ref_init, beta_init, warm, gfl, out); return FB_OK; }
+    catch (const std::exception &e) { g_create_error = e.what(); return FB_ERR_ARG; }
+}
+/* test hook: the scatter front end alone (cts_core.c:5-47: the reference's object in libfbo_ref.so, the restatement in the port) */
+FB_API int fbo_test_cts_core(int nbins, double dispersion, const fb_cts *c, const double *phi, double *phihat, double *phihat_var,
+                             double *phihat_var_nodecay, double *ncounts) {
+    PerfCts cts = perf_copy_cts(c);
+    const int nb = nbins * (nbins + 1) / 2;
+    vec ph(phi, phi + nb);
+    ivec b1(nb), b2(nb);
+    std::fill(phihat, phihat + nb, 0.0); std::fill(phihat_var, phihat_var + nb, 0.0);
+    std::fill(phihat_var_nodecay, phihat_var_nodecay + nb, 0.0); std::fill(ncounts, ncounts + nb, 0.0);
+    ORACLE_CTS_CORE((int)cts.bin1.size(), cts.bin1.data(), cts.bin2.data(), cts.count.data(), cts.lmu_nosig.data(), cts.nobs.data(),
+                    cts.log_decay.data(), nbins, dispersion, ph.data(), phihat, phihat_var, phihat_var_nodecay, ncounts, b1.data(), b2.data());
     return FB_OK;
 }
 FB_API int64_t fbo_kernel_launches(const fb_handle *) { return 0; }
