@@ -8,7 +8,13 @@ stand-in for the reference's R entry points (R is not available in this image):
     fast_binless_difference(out, mat, ref, alpha, lam2, lam1=0, tol_val=0.2, compute_patchnos=True,
                             maxdiag=0)                                   -> dict  (binless:::fast_binless_difference)
 
-Same names, argument meaning, defaults and error behaviour as /root/reference/binless/src/csnorm_cpp.cpp:18-26.
+    wgfl_signal_BIC(cts, dispersion, nouter, nbins, GFLState, lam2, tol_val, metadata, beta, constrained, fixed, positive,
+                    lambda1_fixed, lambda1_fix_value)                    -> dict  (binless:::wgfl_signal_BIC)
+    wgfl_diff_BIC(cts, ref, dispersion, nouter, nbins, GFLState, lam2, tol_val, metadata, phi_ref, beta, constrained,
+                  lambda1_fixed, lambda1_fix_value)                      -> dict  (binless:::wgfl_diff_BIC)
+
+Same names, argument meaning, defaults and error behaviour as /root/reference/binless/src/csnorm_cpp.cpp:18-26 and
+perf_iteration_signal.hpp / perf_iteration_diff.hpp.
 There is no CPU fallback: the CUDA library must load and a GPU must be present.
 """
 from __future__ import annotations
@@ -55,3 +61,19 @@ def fast_binless_difference(out, mat, ref, alpha, lam2, lam1=0.0, tol_val=2e-1, 
                                maxdiag=maxdiag, verbose=verbose)
         res["diagnostics"]["kernel_launches"] = h.kernel_launches()
     return res
+
+
+def wgfl_signal_BIC(cts, dispersion, nouter, nbins, GFLState, lam2, tol_val, metadata, beta, constrained, fixed,
+                    positive=True, lambda1_fixed=False, lambda1_fix_value=0.0):
+    """binless:::wgfl_signal_BIC (perf_iteration_signal.cpp:22-157) on the GPU; `cts` / `metadata` as dicts of columns."""
+    from ._abi import wgfl_signal_bic
+    return wgfl_signal_bic(cuda_lib(), cts, dispersion, nouter, nbins, GFLState, lam2, tol_val, metadata, beta, constrained,
+                           fixed, positive, lambda1_fixed, lambda1_fix_value)
+
+
+def wgfl_diff_BIC(cts, ref, dispersion, nouter, nbins, GFLState, lam2, tol_val, metadata, phi_ref, beta, constrained,
+                  lambda1_fixed=False, lambda1_fix_value=0.0):
+    """binless:::wgfl_diff_BIC (perf_iteration_diff.cpp:20-117) on the GPU."""
+    from ._abi import wgfl_diff_bic
+    return wgfl_diff_bic(cuda_lib(), cts, ref, dispersion, nouter, nbins, GFLState, lam2, tol_val, metadata, phi_ref, beta,
+                         constrained, lambda1_fixed, lambda1_fix_value)

@@ -4,6 +4,7 @@
 #include "fb_model.cuh"
 #include "fb_comm.cuh"
 #include "fb_csv.hpp"
+#include "fb_perf.cuh"
 #include <string>
 
 struct fb_handle {
@@ -87,6 +88,15 @@ FB_API int fb_csv_write(const char *path, const char *header, int64_t nrows, int
     return guarded(fb::g_last_error, [&] {
         if (!fb::write_csv_gz(path, header, nrows, ncols, cols, gzip != 0)) throw fb::ArgError(std::string("cannot write ") + path);
     });
+}
+
+FB_API int fb_wgfl_signal_bic(int nbins, const fb_cts *cts, const fb_perf_meta *meta, const fb_perf_params *p, const double *beta_init,
+                              int warm, fb_gfl_state *gfl, fb_perf_signal_out *out) {
+    return guarded(fb::g_last_error, [&] { fb::wgfl_signal_bic(nbins, cts, meta, p, beta_init, warm, gfl, out); });
+}
+FB_API int fb_wgfl_diff_bic(int nbins, const fb_cts *cts, const fb_cts *ref, const fb_perf_meta *meta, const fb_perf_params *p,
+                            const double *phi_ref_init, const double *beta_init, int warm, fb_gfl_state *gfl, fb_perf_diff_out *out) {
+    return guarded(fb::g_last_error, [&] { fb::wgfl_diff_bic(nbins, cts, ref, meta, p, phi_ref_init, beta_init, warm, gfl, out); });
 }
 
 FB_API int fb_set_interrupt_cb(fb_handle *h, int (*cb)(void *), void *arg) {
