@@ -40,9 +40,10 @@ def cuda_lib() -> FastBinlessLib:
 
 
 def fast_binless(mat, nbins, alpha, lam2, lam1=0.0, nouter=25, tol_val=2e-1, bg_steps=5, free_decay=10000,
-                 compute_patchnos=True, csv_out="", maxdiag=0, verbose=False, columns=True):
-    """binless:::fast_binless (csnorm_cpp.cpp:18-22 -> fast_binless.cpp:85-184) on the GPU."""
-    with cuda_lib().create(mat, nbins) as h:
+                 compute_patchnos=True, csv_out="", maxdiag=0, verbose=False, columns=True, ngpus=1):
+    """binless:::fast_binless (csnorm_cpp.cpp:18-22 -> fast_binless.cpp:85-184) on the GPU; ngpus > 1 shares every
+    fused-lasso solve between that many devices of this process (fb_create_multi)."""
+    with cuda_lib().create(mat, nbins, ngpus) as h:
         out = h.run_signal(alpha, lam2, lam1, columns=columns, nouter=nouter, tol_val=tol_val, bg_steps=bg_steps,
                            free_decay=free_decay, compute_patchnos=compute_patchnos, csv_out=csv_out,
                            maxdiag=maxdiag, verbose=verbose)

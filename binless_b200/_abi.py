@@ -107,7 +107,7 @@ ENTRY_POINTS = ["create", "destroy", "last_error", "run_signal", "restore", "run
                 "eval_cv", "sweep_lambda", "gfl_solve", "set_interrupt_cb", "kernel_launches", "release_cached_memory",
                 "comm_unique_id", "comm_init", "comm_destroy", "comm_rank", "comm_world", "shard_plan",
                 "create_binned", "get_mat", "mat_rows", "cv_score", "csv_write",
-                "wgfl_signal_bic", "wgfl_diff_bic"]
+                "wgfl_signal_bic", "wgfl_diff_bic", "create_multi", "handle_ngpus", "gfl_solve_multi"]
 
 
 def _dp(a):
@@ -187,6 +187,12 @@ class FastBinlessLib:
         self._wgfl_diff_bic.argtypes = [C.c_int, C.POINTER(fb_cts), C.POINTER(fb_cts), C.POINTER(fb_perf_meta),
                                         C.POINTER(fb_perf_params), c_dp, c_dp, C.c_int, C.POINTER(fb_gfl_state), C.POINTER(fb_perf_diff_out)]
         self._wgfl_diff_bic.restype = C.c_int
+        self._create_multi = f("create_multi")
+        self._create_multi.argtypes = [C.c_int, C.POINTER(fb_mat), C.c_int, C.POINTER(C.c_void_p)]; self._create_multi.restype = C.c_int
+        self._gfl_solve_multi = f("gfl_solve_multi")
+        self._gfl_solve_multi.argtypes = [C.c_int, C.c_int, C.c_uint, c_dp, c_dp, C.c_double, C.c_double, C.c_int, C.c_int,
+                                          C.POINTER(fb_gfl_state), c_dp]
+        self._gfl_solve_multi.restype = C.c_int
         self._kernel_launches = f("kernel_launches")
         self._kernel_launches.argtypes = [C.c_void_p]; self._kernel_launches.restype = C.c_int64
         self._gfl_solve = f("gfl_solve")
@@ -263,7 +269,8 @@ class FastBinlessLib:
                                   _dp(cols["distance"]), _ip(cols["observed"]), _ip(cols["nobs"])), None)
         return Handle(self, h, cols, nb.value)
 
-    def create(self, mat, nbins):
+    def create(self, mat, nbins, ngpus=1):
+        """fb_create, or fb_create_multi when ngpus > 1 (one process, one host thread and communicator per device)."""
         cols = {}
         for k in ("name", "bin1", "pos1", "bin2", "pos2", "observed", "nobs"):
             cols[k] = _i32(mat[k]) if mat.get(k) is not None else None
@@ -271,7 +278,8 @@ class FastBinlessLib:
         m = fb_mat(N=cols["distance"].size, distance=_dp(cols["distance"]),
                    **{k: _ip(v) for k, v in cols.items() if k != "distance"})
         h = C.c_void_p()
-        rc = self._create(int(nbins), C.byref(m), C.byref(h))
+        rc = self._create(int(nbins), C.byref(m), C.byref(h)) if int(ngpus) <= 1 else \
+            self._create_multi(int(nbins), C.byref(m), int(ngpus), C.byref(h))
         self._check(rc, None)
         return Handle(self, h, cols, int(nbins))
 
@@ -486,8 +494,9 @@ def wgfl_diff_bic(lib: FastBinlessLib, cts, ref, dispersion, nouter, nbins, gfl_
     return res
 
 
-def gfl_solve(lib: FastBinlessLib, nbins, y, w, lam2, converge, maxsteps=30000, maxdiag=0, state=None):
-    """FusedLassoGaussianEstimator<GFLLibrary>::optimize on one packed triangle."""
+def gfl_solve(lib: FastBinlessLib, nbins, y, w, lam2, converge, maxsteps=30000, maxdiag=0, state=None, ngpus=1):
+    """FusedLassoGaussianEstimator<GFLLibrary>::optimize on one packed triangle (ngpus > 1: shared by that many devices of
+    this process, fb_gfl_solve_multi)."""
     y = _f64(y); w = _f64(w)
     nc = nbins * (nbins + 1) // 2
     md = min(int(maxdiag), nbins)
@@ -506,7 +515,11 @@ def gfl_solve(lib: FastBinlessLib, nbins, y, w, lam2, converge, maxsteps=30000, 
         beta = np.zeros(n_solved); z = np.zeros(tsz); u = np.zeros(tsz); alpha = 5.0
     st = fb_gfl_state(beta=_dp(beta), z=_dp(z), u=_dp(u), alpha=alpha, steps=0)
     full = np.empty(nc)
-    rc = lib._gfl_solve(int(nbins), int(maxdiag), _dp(y), _dp(w), float(lam2), float(converge), int(maxsteps),
-                        int(warm), C.byref(st), _dp(full))
+    if int(ngpus) > 1:
+        rc = lib._gfl_solve_multi(int(ngpus), int(nbins), int(maxdiag), _dp(y), _dp(w), float(lam2), float(converge), int(maxsteps),
+                                  int(warm), C.byref(st), _dp(full))
+    else:
+        rc = lib._gfl_solve(int(nbins), int(maxdiag), _dp(y), _dp(w), float(lam2), float(converge), int(maxsteps),
+                            int(warm), C.byref(st), _dp(full))
     lib._check(rc, None)
     return dict(beta=beta, z=z, u=u, alpha=st.alpha, steps=st.steps, beta_full=full)

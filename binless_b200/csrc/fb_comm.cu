@@ -32,7 +32,9 @@ const char *kNames[] = {"ncclGetUniqueId", "ncclCommInitRank", "ncclCommDestroy"
             throw CommError(std::string(#call) + " failed: " + reinterpret_cast<fn_errstr>(fn_[F_ERRSTR])(_r)); \
     } while (0)
 
-Comm &Comm::get() { static Comm c; return c; }
+namespace { thread_local Comm *tl_current = nullptr; }
+Comm &Comm::get() { static Comm process_wide; return tl_current ? *tl_current : process_wide; }
+void Comm::set_current(Comm *c) { tl_current = c; }
 
 void Comm::load() {
     if (lib_) return;

@@ -21,7 +21,13 @@ void shard_plan(int n, int md, int world, int *row_begin, int *col_begin);
 
 class Comm {
 public:
+    // the communicator of the calling host thread: the process-wide one (one process per GPU), or the one a rank thread
+    // of a single-process multi-GPU handle installed with set_current (fb_create_multi: one host thread per device)
     static Comm &get();
+    static void set_current(Comm *c);
+    Comm() {}
+    Comm(const Comm &) = delete;
+    Comm &operator=(const Comm &) = delete;
     bool active() const { return comm_ != nullptr && world_ > 1; }
     int rank() const { return rank_; }
     int world() const { return world_; }

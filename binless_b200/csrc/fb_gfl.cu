@@ -41,6 +41,7 @@ using namespace taut;
 // --------------------------------------------------------------------------
 // beta update (update_beta_weight, gfl_graph_fl.c:241-264)
 // --------------------------------------------------------------------------
+#ifdef FB_BETA_V1
 __global__ void __launch_bounds__(TILE * 8)
 k_beta(Grid g, const GflCtl *__restrict__ ctl, const double *__restrict__ y, const double *__restrict__ w,
        const double *__restrict__ zr, double *__restrict__ ur, const double *__restrict__ zc,
@@ -102,6 +103,89 @@ k_beta(Grid g, const GflCtl *__restrict__ ctl, const double *__restrict__ y, con
         if (j < g.n && i <= j && j - i < g.md && j >= 1) betaT[g.cm(i, j)] = s_beta[tx][jj];
     }
 }
+#else
+// Every global load of the tile is issued before the first use (24 per thread in flight): ncu showed the first version
+// stalled on the long scoreboard 61 % of the time with a handful of loads per warp outstanding.
+__global__ void __launch_bounds__(TILE * 8)
+k_beta(Grid g, const GflCtl *__restrict__ ctl, const double *__restrict__ y, const double *__restrict__ w,
+       const double *__restrict__ zr, double *__restrict__ ur, const double *__restrict__ zc,
+       double *__restrict__ uc, double *__restrict__ beta, double *__restrict__ betaT,
+       const int r0, const int r1, const int c0, const int c1) {
+    if (ctl->done) return;
+    const int i0 = blockIdx.y * TILE, j0 = blockIdx.x * TILE;
+    // tile must intersect the band 0 <= j-i < md
+    if (j0 + TILE - 1 < i0 || j0 - (i0 + TILE - 1) >= g.md) return;
+    // ... and hold a cell of a chain this rank owns (rows [r0, r1) or columns [c0, c1); everything when not sharded)
+    if (!(i0 < r1 && i0 + TILE > r0) && !(j0 < c1 && j0 + TILE > c0)) return;
+    __shared__ double s_tcol[TILE][TILE + 1]; // z_col - u_col, indexed [j][i]
+    __shared__ double s_beta[TILE][TILE + 1]; // indexed [i][j]
+    const int tx = threadIdx.x, ty = threadIdx.y;
+    const double alpha = ctl->alpha, inflate = ctl->inflate;
+    const int mode = ctl->rescale;
+    if (!y) { y = ctl->y; w = ctl->w; }   // captured iteration: the inputs of the current solve
+    constexpr int NQ = TILE / 8;
+    // column-major side: cell (i0 + tx, j0 + ty + 8 q); row-major side: cell (i0 + ty + 8 q, j0 + tx)
+    int64_t cidx[NQ], ridx[NQ];
+    bool cok[NQ], rok[NQ], hrow[NQ];
+    double vuc[NQ], vzc[NQ], vur[NQ], vzr[NQ], vw[NQ], vy[NQ];
+#pragma unroll
+    for (int q = 0; q < NQ; ++q) {
+        const int j = j0 + ty + 8 * q, i = i0 + tx;
+        cok[q] = j < g.n && i <= j && j - i < g.md && j >= 1;
+        cidx[q] = cok[q] ? g.cm(i, j) : 0;
+        const int i2 = i0 + ty + 8 * q, j2 = j0 + tx;
+        rok[q] = j2 < g.n && i2 <= j2 && j2 - i2 < g.md;
+        ridx[q] = rok[q] ? g.rm(i2, j2) : 0;
+        hrow[q] = rok[q] && i2 <= g.n - 2;
+    }
+#pragma unroll
+    for (int q = 0; q < NQ; ++q) {
+        vuc[q] = cok[q] ? uc[cidx[q]] : 0.0; vzc[q] = cok[q] ? zc[cidx[q]] : 0.0;
+        vur[q] = hrow[q] ? ur[ridx[q]] : 0.0; vzr[q] = hrow[q] ? zr[ridx[q]] : 0.0;
+        vw[q] = rok[q] ? w[ridx[q]] : 0.0; vy[q] = rok[q] ? y[ridx[q]] : 0.0;
+    }
+    // phase A: column duals into the transposition tile
+#pragma unroll
+    for (int q = 0; q < NQ; ++q) {
+        double t = 0.0;
+        if (cok[q]) {
+            double u = vuc[q];
+            if (mode == 1) { u = u / inflate; uc[cidx[q]] = u; }
+            else if (mode == 2) { u = u * inflate; uc[cidx[q]] = u; }
+            t = vzc[q] - u;
+        }
+        s_tcol[ty + 8 * q][tx] = t;
+    }
+    __syncthreads();
+    // phase B: row duals + beta
+#pragma unroll
+    for (int q = 0; q < NQ; ++q) {
+        const int ii = ty + 8 * q;
+        double b = 0.0;
+        if (rok[q]) {
+            const bool has_col = (j0 + tx >= 1);
+            double r = 0.0;
+            if (hrow[q]) {
+                double u = vur[q];
+                if (mode == 1) { u = u / inflate; ur[ridx[q]] = u; }
+                else if (mode == 2) { u = u * inflate; ur[ridx[q]] = u; }
+                r += vzr[q] - u;
+            }
+            if (has_col) r += s_tcol[tx][ii];
+            const int nz = (hrow[q] ? 1 : 0) + (has_col ? 1 : 0);
+            const double wi = vw[q];
+            b = (2.0 * vy[q] * wi + alpha * r) / (2.0 * wi + alpha * nz);
+            beta[ridx[q]] = b;
+        }
+        s_beta[ii][tx] = b;
+    }
+    __syncthreads();
+    // phase C: column-major copy of beta, coalesced along i
+#pragma unroll
+    for (int q = 0; q < NQ; ++q)
+        if (cok[q]) betaT[cidx[q]] = s_beta[tx][ty + 8 * q];
+}
+#endif
 
 // --------------------------------------------------------------------------
 // chain prox: one warp per chain, exact taut string. For the chain v_0..v_{L-1} (v = beta + u) and

@@ -31,17 +31,40 @@ PhaseTimer g_pt;
 const char *kLayoutMsg = "pos1/pos2 do not depend on the bin only or distance not on bin2-bin1 only";   // -> per-cell fallback
 const char *kSizeMsg = "Input size should be N(N+1)/2 dense matrix of observed counts for each dataset";
 
+// make_even_bins (util.cpp:56-68) as a sorted edge list: (edge value, index). The reference keeps the edges in a
+// std::map, so equal edge values (a degenerate range) keep the LAST index assigned; that case goes through a map here
+// too, the usual strictly increasing edges do not need one.
+struct EvenBins {
+    std::vector<double> key; std::vector<unsigned> val; unsigned Nbins;
+    EvenBins(double lower, double upper, unsigned Nb) : Nbins(Nb) {
+        const double size = upper - lower;
+        key.resize(Nb + 1); val.resize(Nb + 1);
+        bool increasing = true;
+        for (unsigned i = 0; i <= Nb; ++i) {
+            key[i] = lower + i * size / double(Nb); val[i] = i;
+            if (i && !(key[i] > key[i - 1])) increasing = false;
+        }
+        if (!increasing) {
+            std::map<double, unsigned> edges;
+            for (unsigned i = 0; i <= Nb; ++i) edges[lower + i * size / double(Nb)] = i;
+            key.clear(); val.clear();
+            for (auto &kv : edges) { key.push_back(kv.first); val.push_back(kv.second); }
+        }
+    }
+    int bin(double v) const {   // bin_data (util.cpp:70-81): upper_bound, past the end -> last bin
+        const size_t k = std::upper_bound(key.begin(), key.end(), v) - key.begin();
+        return (int)((k == key.size() ? val.back() : val[k]) - 1);
+    }
+};
+
 // make_even_bins + bin_data with drop=true (util.cpp:56-111): bin index of each value, unused bins removed
 std::vector<int> even_bins_dropped(const std::vector<double> &v, double lower, double upper, unsigned Nbins, int &nkept) {
-    std::map<double, unsigned> edges;
-    const double size = upper - lower;
-    for (unsigned i = 0; i <= Nbins; ++i) edges[lower + i * size / double(Nbins)] = i;
+    const EvenBins eb(lower, upper, Nbins);
     std::vector<int> raw(v.size());
     std::vector<char> used(Nbins, 0);
     for (size_t k = 0; k < v.size(); ++k) {
-        auto it = edges.upper_bound(v[k]);
-        const unsigned j = (it == edges.end()) ? edges.rbegin()->second - 1 : it->second - 1;
-        raw[k] = (int)j;
+        const int j = eb.bin(v[k]);
+        raw[k] = j;
         used[j] = 1;
     }
     std::vector<int> remap(Nbins, -1);
@@ -235,21 +258,6 @@ void Model::ingest(int nbins, const fb_mat *m) {
 }
 
 namespace {
-// make_even_bins (util.cpp:56-68) as a sorted edge list: (edge value, index); equal edges keep the LAST index like the
-// std::map assignment of the reference
-struct EvenBins {
-    std::vector<double> key; std::vector<unsigned> val; unsigned Nbins;
-    EvenBins(double lower, double upper, unsigned Nb) : Nbins(Nb) {
-        std::map<double, unsigned> edges;
-        const double size = upper - lower;
-        for (unsigned i = 0; i <= Nb; ++i) edges[lower + i * size / double(Nb)] = i;
-        for (auto &kv : edges) { key.push_back(kv.first); val.push_back(kv.second); }
-    }
-    int bin(double v) const {   // bin_data (util.cpp:70-81): upper_bound, past the end -> last bin
-        const size_t k = std::upper_bound(key.begin(), key.end(), v) - key.begin();
-        return (int)((k == key.size() ? val.back() : val[k]) - 1);
-    }
-};
 template <class F>
 void par_for(int64_t N, F &&fn) {   // fn(lo, hi) on host_threads() contiguous ranges
     const int nthr = host_threads();
@@ -340,48 +348,40 @@ void Model::ingest_cells(const fb_mat *m) {
 // ---------------------------------------------------------------------------------------------
 // legs
 // ---------------------------------------------------------------------------------------------
+// The binners and the observables per leg bin are functions of the matrix alone (SummarizerSettingsImpl constructors,
+// fast_exposure.hpp:35-51, fast_bias_mean.hpp:37-68, fast_decay.hpp:48-68): built on the first call of a handle and kept
+// with it, like the uploaded matrix. What depends on the call (the GAM settings, the zeroed estimates) is redone.
 void Model::build_legs(double tol_val, unsigned free_decay) {
     const int n = t_.n, D = t_.D;
-    if (generic_) {   // the binners were evaluated cell by cell at ingest
-        dec_.setup(dec_support_, dec_smin_, dec_smax_, tol_val, free_decay);
+    if (!struct_built_) {
+        if (!generic_) {
+            // bias binner (fast_bias_mean.hpp:37-68): even bins between min and max position
+            const double mn = *std::min_element(pos_.begin(), pos_.end()), mx = *std::max_element(pos_.begin(), pos_.end());
+            rowbin_ = even_bins_dropped(pos_, mn, mx, (unsigned)n, nb_bias_);
+            // decay binner (fast_decay.hpp:48-68): K * bins_per_bf even bins of log(distance), empty ones dropped
+            std::vector<double> ld(n);
+            for (int k = 0; k < n; ++k) ld[k] = std::log(dist_[k]);
+            dec_smin_ = *std::min_element(ld.begin(), ld.end()); dec_smax_ = *std::max_element(ld.begin(), ld.end());
+            dbin_ = even_bins_dropped(ld, dec_smin_, dec_smax_, (unsigned)(kDecayK * kDecayBinsPerBf), nb_dec_);
+            std::vector<double> sup_num(nb_dec_, 0.0), sup_den(nb_dec_, 0.0);
+            for (int k = 0; k < n; ++k) { // mean log-distance per bin over all cells: D*(n-k) cells on diagonal k
+                const double cnt = (double)D * (double)(n - k);
+                sup_num[dbin_[k]] += cnt * ld[k]; sup_den[dbin_[k]] += cnt;
+            }
+            dec_support_.resize(nb_dec_);
+            for (int b = 0; b < nb_dec_; ++b) dec_support_[b] = sup_num[b] / sup_den[b];
+        }   // else: the binners were evaluated cell by cell at ingest (ingest_cells)
+        // observables per leg bin (integers: exact in any order)
         std::vector<double> dummy;
-        std::fill(tab_h_.p, tab_h_.p + tab_h_.n, 0.0);
-        FB_CUDA(cudaMemcpyAsync(tab_.p, tab_h_.p, tab_h_.n * sizeof(double), cudaMemcpyHostToDevice, st_));
         leg_sums(LEG_EXPO, MODE_NOBS, expo_nobs_, dummy);
         leg_sums(LEG_DECAY, MODE_NOBS, dec_nobs_, dummy);
         leg_sums(LEG_BIAS, MODE_NOBS, bias_nobs_, dummy);
         for (auto &v : bias_nobs_) v = v / 2.; // fast_bias_mean.hpp:58
-        expo_est_.assign(D, 0.0);
-        bias_est_.assign(nb_bias_, 0.0);
-        legs_built_ = true;
-        return;
+        struct_built_ = true;
     }
-    // bias binner (fast_bias_mean.hpp:37-68): even bins between min and max position
-    {
-        const double mn = *std::min_element(pos_.begin(), pos_.end()), mx = *std::max_element(pos_.begin(), pos_.end());
-        rowbin_ = even_bins_dropped(pos_, mn, mx, (unsigned)n, nb_bias_);
-    }
-    // decay binner (fast_decay.hpp:48-68): K * bins_per_bf even bins of log(distance), empty ones dropped
-    std::vector<double> ld(n);
-    for (int k = 0; k < n; ++k) ld[k] = std::log(dist_[k]);
-    const double smin = *std::min_element(ld.begin(), ld.end()), smax = *std::max_element(ld.begin(), ld.end());
-    dbin_ = even_bins_dropped(ld, smin, smax, (unsigned)(kDecayK * kDecayBinsPerBf), nb_dec_);
-    std::vector<double> sup_num(nb_dec_, 0.0), sup_den(nb_dec_, 0.0);
-    for (int k = 0; k < n; ++k) { // mean log-distance per bin over all cells: D*(n-k) cells on diagonal k
-        const double cnt = (double)D * (double)(n - k);
-        sup_num[dbin_[k]] += cnt * ld[k]; sup_den[dbin_[k]] += cnt;
-    }
-    std::vector<double> support(nb_dec_);
-    for (int b = 0; b < nb_dec_; ++b) support[b] = sup_num[b] / sup_den[b];
-    dec_.setup(support, smin, smax, tol_val, free_decay);
-    // observables per leg bin (integers: exact in any order)
-    std::vector<double> dummy;
+    dec_.setup(dec_support_, dec_smin_, dec_smax_, tol_val, free_decay);
     std::fill(tab_h_.p, tab_h_.p + tab_h_.n, 0.0);
     FB_CUDA(cudaMemcpyAsync(tab_.p, tab_h_.p, tab_h_.n * sizeof(double), cudaMemcpyHostToDevice, st_));
-    leg_sums(LEG_EXPO, MODE_NOBS, expo_nobs_, dummy);
-    leg_sums(LEG_DECAY, MODE_NOBS, dec_nobs_, dummy);
-    leg_sums(LEG_BIAS, MODE_NOBS, bias_nobs_, dummy);
-    for (auto &v : bias_nobs_) v = v / 2.; // fast_bias_mean.hpp:58
     expo_est_.assign(D, 0.0);
     bias_est_.assign(nb_bias_, 0.0);
     legs_built_ = true;

@@ -64,7 +64,7 @@ private:
     std::vector<double> pos_;   // [n] position of bin r
     std::vector<double> dist_;  // [n] distance of diagonal k
     // legs (host side; all O(n))
-    bool legs_built_ = false, has_state_ = false;
+    bool legs_built_ = false, has_state_ = false, struct_built_ = false;
     double alpha_ = 1.0;
     int nb_bias_ = 0, nb_dec_ = 0;
     std::vector<int> rowbin_, dbin_;                  // row -> bias bin, diagonal -> decay bin

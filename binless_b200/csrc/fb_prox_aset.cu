@@ -179,6 +179,31 @@ k_prox_aset(GflCtl *__restrict__ ctl, const AsChain *__restrict__ chains, const 
             }
             __syncthreads();
             if (stats) tc2 = clock64();
+#ifndef FB_AS_NO_PREFETCH
+            // the next batch of this CTA is known (queue head fetched at the top): ask L2 for its beta / u / z lines now,
+            // so that the staging loads of the next round find them there instead of paying the HBM latency
+            {
+                const int bnext = s.ci[C_BATCH];
+                if (bnext < nbatches) {
+                    const AsBatch nb = batches[bnext];
+                    if (tid < (nb.npts >> 5)) {
+                        const AsWord d = words[nb.w0 + tid];
+                        if (d.nvalid > 0) {
+                            const double *pb = (nb.dir == 0 ? beta : betaT) + d.goff, *pu = (nb.dir == 0 ? ur : uc) + d.goff,
+                                         *pz = (nb.dir == 0 ? zr : zc) + d.goff;
+                            const int last = d.nvalid - 1;
+#pragma unroll
+                            for (int q = 0; q < 3; ++q) {
+                                const int o = q == 0 ? 0 : (q == 1 ? min(16, last) : last);
+                                asm volatile("prefetch.global.L2 [%0];" ::"l"(pb + o));
+                                asm volatile("prefetch.global.L2 [%0];" ::"l"(pu + o));
+                                asm volatile("prefetch.global.L2 [%0];" ::"l"(pz + o));
+                            }
+                        }
+                    }
+                }
+            }
+#endif
             // ---- P: passes until no knot changes ----
             if (tid < AS_TWN) {     // the first pass looks at every word
                 const int left = nwu - (tid << 5);

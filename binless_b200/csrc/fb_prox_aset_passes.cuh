@@ -21,7 +21,10 @@ constexpr int AS_NT = 256, AS_NW = AS_NT / 32;
 constexpr int AS_RT = 256;                      // reciprocal table R[m] = 1/m
 constexpr int AS_PB = 9, AS_PW = 32 * AS_PB;    // blocked prefix sums: AS_PB consecutive points per lane (odd: no bank conflicts)
 constexpr int AS_SPLIT = 2 * AS_PW;             // chains longer than this are scanned by all warps of the CTA
-constexpr int AS_UN = 2;                        // words whose global loads are in flight together per warp
+#ifndef FB_AS_UN
+#define FB_AS_UN 2
+#endif
+constexpr int AS_UN = FB_AS_UN;                 // words whose global loads are in flight together per warp
 constexpr double AS_EPS = 0x1p-46;              // rounding margin of the tube test (see pass_points)
 enum { C_BATCH = 0, C_COUNT = 4 };
 constexpr int AS_TWN = 8;                       // 32-word blocks of the active-word masks (256 words)

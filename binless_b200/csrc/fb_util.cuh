@@ -64,7 +64,16 @@ public:
         for (auto &kv : free_) { if (pinned_) cudaFreeHost(kv.second); else cudaFree(kv.second); }
         free_.clear(); cached_ = 0;
     }
-    static BlockCache &device() { static BlockCache c(false); return c; }
+    // one cache per device: a single-process multi-GPU handle runs one host thread per device (fb_create_multi)
+    static BlockCache &device() {
+        static BlockCache c[16] = {BlockCache(false), BlockCache(false), BlockCache(false), BlockCache(false), BlockCache(false),
+                                   BlockCache(false), BlockCache(false), BlockCache(false), BlockCache(false), BlockCache(false),
+                                   BlockCache(false), BlockCache(false), BlockCache(false), BlockCache(false), BlockCache(false),
+                                   BlockCache(false)};
+        int dev = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess) { cudaGetLastError(); dev = 0; }
+        return c[dev & 15];
+    }
     static BlockCache &host() { static BlockCache c(true); return c; }
 private:
     bool pinned_;

@@ -311,6 +311,18 @@ FB_API int FB_NAME(comm_rank)(void);
 FB_API int FB_NAME(comm_world)(void);
 FB_API int FB_NAME(shard_plan)(int nbins, unsigned maxdiag, int world, int32_t *row_begin, int32_t *col_begin);
 
+/* Multi-GPU from ONE process (the reference entry point is one R call in one process,
+ * csnorm_cpp.cpp:18-22): the handle holds one copy of the matrix per device (devices 0 .. ngpus-1 of the visible ones);
+ * every fb_run_* / fb_restore / fb_eval_cv / fb_sweep_lambda / fb_cv_score call on it is executed by ngpus host threads,
+ * one per device, each with its own NCCL communicator, sharing every fused-lasso solve exactly as ngpus processes
+ * would after fb_comm_init (trail blocks; results identical bit for bit to one GPU). The caller sees rank 0's outputs.
+ * ngpus == 1 is fb_create. fb_set_interrupt_cb is refused on such a handle. fb_gfl_solve_multi: the stand-alone solve. */
+FB_API int FB_NAME(create_multi)(int nbins, const fb_mat *mat, int ngpus, fb_handle **out);
+FB_API int FB_NAME(handle_ngpus)(const fb_handle *h);
+FB_API int FB_NAME(gfl_solve_multi)(int ngpus, int nbins, unsigned maxdiag, const double *y, const double *w,
+                                    double lam2, double converge, int maxsteps, int warm,
+                                    fb_gfl_state *st, double *beta_full);
+
 FB_API int FB_NAME(set_interrupt_cb)(fb_handle *h, int (*cb)(void *), void *arg);
 
 /* Diagnostics: number of CUDA kernels launched by the last run_* / eval_cv call on this handle

@@ -1422,6 +1422,16 @@ FB_API int fbo_comm_init(int rank, int world, const void *) {
     g_create_error = "the CPU oracle is a single rank"; return 6;
 }
 FB_API int fbo_comm_destroy(void) { return FB_OK; }
+/* single-process multi-GPU entry points: the reference is one thread on one CPU, so "ngpus" changes nothing here */
+FB_API int fbo_create(int nbins, const fb_mat *mat, fb_handle **out);
+FB_API int fbo_create_multi(int nbins, const fb_mat *mat, int, fb_handle **out) { return fbo_create(nbins, mat, out); }
+FB_API int fbo_handle_ngpus(const fb_handle *h) { return h ? 1 : 0; }
+FB_API int fbo_gfl_solve(int nbins, unsigned maxdiag, const double *y, const double *w, double lam2,
+                         double converge, int maxsteps, int warm, fb_gfl_state *st, double *beta_full);
+FB_API int fbo_gfl_solve_multi(int, int nbins, unsigned maxdiag, const double *y, const double *w, double lam2,
+                               double converge, int maxsteps, int warm, fb_gfl_state *st, double *beta_full) {
+    return fbo_gfl_solve(nbins, maxdiag, y, w, lam2, converge, maxsteps, warm, st, beta_full);
+}
 FB_API int fbo_comm_rank(void) { return 0; }
 FB_API int fbo_comm_world(void) { return 1; }
 FB_API int fbo_shard_plan(int nbins, unsigned maxdiag, int world, int32_t *row_begin, int32_t *col_begin) {

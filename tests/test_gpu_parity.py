@@ -402,6 +402,39 @@ def test_trail_block_sharding_on_two_gpus():
 
 
 @pytest.mark.timeout(600)
+def test_single_process_multi_gpu_is_bit_identical(gpu_lib):
+    """fb_create_multi / fb_gfl_solve_multi (multi-GPU chosen by the caller of ONE process, as a stock R session
+    would): one host thread and one NCCL communicator per device share every fused-lasso solve; the results must equal the
+    single-GPU ones bit for bit. Needs two devices."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (run on a --gpus 2 box)")
+    from binless_b200.dist import _nccl_library_path
+    if "FB_NCCL_LIB" not in os.environ and _nccl_library_path():
+        os.environ["FB_NCCL_LIB"] = _nccl_library_path()
+    n = 300
+    rng = np.random.default_rng(7)
+    nc = n * (n + 1) // 2
+    y = np.repeat(rng.normal(0, 1, nc // 25 + 1), 25)[:nc] + rng.normal(0, 0.4, nc); w = rng.uniform(0, 3, nc)
+    a = gfl_solve(gpu_lib, n, y, w, 2.5, 1e-12, 20, 0)
+    b = gfl_solve(gpu_lib, n, y, w, 2.5, 1e-12, 20, 0, ngpus=2)
+    assert a["steps"] == b["steps"] and a["alpha"] == b["alpha"]
+    for k in ("beta", "z", "u", "beta_full"):
+        assert np.array_equal(a[k], b[k]), k
+    mat = synth(96, 2, 5000, 4)
+    with gpu_lib.create(mat, 96) as h1:
+        o1 = h1.run_signal(0.5, 2.5, 0.1)
+        d1 = h1.run_difference(1, 0.5, 3.0, 0.1)
+    with gpu_lib.create(mat, 96, ngpus=2) as h2:
+        o2 = h2.run_signal(0.5, 2.5, 0.1)
+        d2 = h2.run_difference(1, 0.5, 3.0, 0.1)
+    assert list(o1["diagnostics"]["solve_iters"]) == list(o2["diagnostics"]["solve_iters"])
+    for k in ("log_signal", "phihat", "weight", "signal", "binless", "background", "biasmat", "decaymat", "patchno"):
+        assert np.array_equal(o1[k], o2[k]), k
+    for k in ("difference", "deltahat", "weight", "phi_ref", "patchno"):
+        assert np.array_equal(d1[k], d2[k]), k
+
+
 @pytest.mark.parametrize("prox", ["aset", "team"])
 def test_gfl_4300_bins_matches_oracle(gpu_lib, oracle, monkeypatch, prox):
     """4300 bins, eight ADMM iterations against the oracle (~10 s of CPU). aset: one chain per batch (two CTAs per
