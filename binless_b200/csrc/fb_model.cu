@@ -117,6 +117,7 @@ void Model::open_stream() {
     FB_CUDA(cudaEventCreate(&ev1_));
 }
 void Model::close_stream() {
+    flo_.reset();
     if (st_) cudaStreamSynchronize(st_); // buffers go back to the block cache only when nothing uses them any more
     if (ev0_) cudaEventDestroy(ev0_);
     if (ev1_) cudaEventDestroy(ev1_);
@@ -489,6 +490,19 @@ void Model::fit_decay(int mode) {
     upload_tables();
 }
 
+// The fused-lasso object of a call: a FRESH FusedLassoGaussianEstimator<GFLLibrary> in the reference (fast_binless.cpp:122).
+// Its structure (chain batches, the captured ADMM graph, the device arrays) depends on (nbins, maxdiag) only, so the handle
+// keeps one and hands it out reset to the cold state (beta = z = u = 0, alpha = 5, counters 0).
+GflSolver &Model::solver(unsigned maxdiag) {
+    if (!flo_ || flo_maxdiag_ != maxdiag || flo_comm_ != (Comm::get().active() ? Comm::get().world() : 1)) {
+        flo_.reset();
+        flo_.reset(new GflSolver(t_.n, maxdiag, st_));
+        flo_maxdiag_ = maxdiag; flo_comm_ = Comm::get().active() ? Comm::get().world() : 1;
+    } else flo_->reset();
+    flo_->kernel_launches = 0;
+    return *flo_;
+}
+
 void Model::check_interrupt() {
     if (interrupt_cb && interrupt_cb(interrupt_arg)) throw Interrupted("interrupted");
 }
@@ -614,7 +628,7 @@ void Model::run_signal(const fb_params *p, fb_signal_out *out) {
     fit_bias(MODE_POISSON);
 
     double current_tol_val = 1.;
-    GflSolver flo(n, p->maxdiag, st_); // shared by all datasets: the flos copies share one strategy (GFLLibrary.hpp:59)
+    GflSolver &flo = solver(p->maxdiag); // shared by all datasets: the flos copies share one strategy (GFLLibrary.hpp:59)
     double flo_tol = current_tol_val / 20.;
     const std::vector<double> lam2 = broadcast(p->lam2, p->n_lam2, D);
     const std::vector<double> lam1 = broadcast(p->lam1, p->n_lam1, D);
@@ -759,7 +773,7 @@ void Model::run_difference(int ref, const fb_params *p, fb_diff_out *out) {
     kernel_launches = 0;
     FB_CUDA(cudaEventRecord(ev0_, st_));
     const double converge = p->tol_val / 20.;
-    GflSolver flo(n, p->maxdiag, st_);
+    GflSolver &flo = solver(p->maxdiag);
     const std::vector<double> lam2 = broadcast(p->lam2, p->n_lam2, D - 1);
     if (p->verbose) std::printf("compute\n");
     DevBuf<double> phihat(N), deltahat(N), w(N), delta(N), colbuf(N);
@@ -811,7 +825,7 @@ void Model::eval_cv(const fb_params *p, int nlam, const double *lam2v, unsigned 
     const std::vector<double> lam1 = broadcast(p->lam1, p->n_lam1, 1);
     DevBuf<double> lam1_d(1), phi_cv(N), y(N), w(N), sig(N), binl(N);
     lam1_d.upload(lam1.data(), 1, st_);
-    GflSolver flo(n, p->maxdiag, st_); // not reset between lambdas: warm-start chain of the reference
+    GflSolver &flo = solver(p->maxdiag); // not reset between lambdas: warm-start chain of the reference
     for (int k = 0; k < nlam; ++k) {
         check_interrupt();
         signal_yw(t_, tables(tab_), alpha_, obs_.p, nobs_.p, phi_.p, group, y.p, w.p, st_);
@@ -846,7 +860,7 @@ void Model::sweep_lambda(const fb_params *p, int nlam, const double *lam2v, fb_s
     PinBuf<double> res_h; res_h.alloc(2);
     signal_yw(t_, tables(tab_), alpha_, obs_.p, nobs_.p, phi_.p, 0, y.p, w.p, st_);
     kernel_launches += 1;
-    GflSolver flo(n, p->maxdiag, st_);
+    GflSolver &flo = solver(p->maxdiag);
     double ms_solver = 0;
     int64_t cell_iters = 0;
     for (int k = 0; k < nlam; ++k) {
@@ -892,7 +906,7 @@ void Model::cv_score(const fb_params *p, int nlam, const double *lam2v, fb_cv_sc
     PinBuf<double> res_h; res_h.alloc(4);
     signal_yw(t_, tables(tab_), alpha_, obs_.p, nobs_.p, phi_.p, 0, y.p, w.p, st_);
     kernel_launches += 1;
-    GflSolver flo(n, p->maxdiag, st_);
+    GflSolver &flo = solver(p->maxdiag);
     double ms_solver = 0;
     int64_t cell_iters = 0;
     std::vector<int> steps((size_t)std::max(1, nlam) * D * 2, 0);

@@ -94,6 +94,9 @@ private:
         if (generic_) { L.cb1 = cb1_.p; L.cb2 = cb2_.p; L.cdb = cdb_.p; }
         return L;
     }
+    std::unique_ptr<GflSolver> flo_;                  // kept across calls (structure only; every call starts from reset())
+    unsigned flo_maxdiag_ = 0; int flo_comm_ = 1;
+    GflSolver &solver(unsigned maxdiag);
     void open_stream();
     void close_stream();
     void ingest_cells(const fb_mat *mat);
