@@ -1,6 +1,7 @@
 // fb_model.cu -- host driver of the fast-binless path (see fb_model.cuh).
 #include "fb_model.cuh"
 #include "fb_csv.hpp"
+#include "fb_comm.cuh"
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
