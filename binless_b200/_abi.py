@@ -99,6 +99,16 @@ class fb_perf_diff_out(C.Structure):
                 ("admm_iters", C.c_int64)]
 
 
+class fb_band_params(C.Structure):
+    _fields_ = [("far_cutoff", C.c_double), ("maxdiag", C.c_uint), ("lam1_final", C.c_double), ("lam1", c_dp), ("n_lam1", C.c_int)]
+
+
+class fb_band_out(C.Structure):
+    _fields_ = [("lam1_sig", c_dp), ("nband", C.c_int64), ("band_bin1", c_ip), ("band_bin2", c_ip), ("band_observed", c_dp),
+                ("band_binless", c_dp), ("sig_cap", C.c_int64), ("nsig", C.POINTER(C.c_int64)), ("sig_bin1", c_ip),
+                ("sig_bin2", c_ip), ("sig_log10", c_dp)]
+
+
 class fb_gfl_state(C.Structure):
     _fields_ = [("beta", c_dp), ("z", c_dp), ("u", c_dp), ("alpha", C.c_double), ("steps", C.c_int)]
 
@@ -107,7 +117,8 @@ ENTRY_POINTS = ["create", "destroy", "last_error", "run_signal", "restore", "run
                 "eval_cv", "sweep_lambda", "gfl_solve", "set_interrupt_cb", "kernel_launches", "release_cached_memory",
                 "comm_unique_id", "comm_init", "comm_destroy", "comm_rank", "comm_world", "shard_plan",
                 "create_binned", "get_mat", "mat_rows", "cv_score", "csv_write",
-                "wgfl_signal_bic", "wgfl_diff_bic", "create_multi", "handle_ngpus", "gfl_solve_multi"]
+                "wgfl_signal_bic", "wgfl_diff_bic", "create_multi", "handle_ngpus", "gfl_solve_multi",
+                "band_export"]
 
 
 def _dp(a):
@@ -193,6 +204,8 @@ class FastBinlessLib:
         self._gfl_solve_multi.argtypes = [C.c_int, C.c_int, C.c_uint, c_dp, c_dp, C.c_double, C.c_double, C.c_int, C.c_int,
                                           C.POINTER(fb_gfl_state), c_dp]
         self._gfl_solve_multi.restype = C.c_int
+        self._band_export = f("band_export")
+        self._band_export.argtypes = [C.c_void_p, C.POINTER(fb_band_params), C.POINTER(fb_band_out)]; self._band_export.restype = C.c_int
         self._kernel_launches = f("kernel_launches")
         self._kernel_launches.argtypes = [C.c_void_p]; self._kernel_launches.restype = C.c_int64
         self._gfl_solve = f("gfl_solve")
@@ -423,7 +436,28 @@ def _cv_score_impl(self, alpha, lam2, lam1=0.0, tol_val=0.2, maxdiag=0):
             "admm_cell_iters": int(o.admm_cell_iters)}
 
 
+def _band_export_impl(self, far_cutoff, maxdiag, lam1=0.0, lam1_final=0.0):
+    """chromosome_binless post-processing (fb_band_export): lam1_sig per dataset, the band triplets (bin1, bin2, observed,
+    binless) and the sparse log10-signal triplets per dataset (R/chromosome.R:262-330)."""
+    l1 = _f64(np.atleast_1d(lam1))
+    p = fb_band_params(far_cutoff=float(far_cutoff), maxdiag=int(maxdiag), lam1_final=float(lam1_final), lam1=_dp(l1), n_lam1=l1.size)
+    D = self.ndatasets
+    sig = np.empty(D); nsig = np.zeros(D, dtype=np.int64)
+    o = fb_band_out(lam1_sig=_dp(sig), nsig=nsig.ctypes.data_as(C.POINTER(C.c_int64)))
+    self.lib._check(self.lib._band_export(self.h, C.byref(p), C.byref(o)), self.h)        # sizes
+    nband, tot = int(o.nband), int(nsig.sum())
+    b1 = np.empty(nband, dtype=np.int32); b2 = np.empty(nband, dtype=np.int32)
+    bo = np.empty((D, nband)); bb = np.empty((D, nband))
+    s1 = np.empty(max(tot, 1), dtype=np.int32); s2 = np.empty(max(tot, 1), dtype=np.int32); sv = np.empty(max(tot, 1))
+    o = fb_band_out(lam1_sig=_dp(sig), nsig=nsig.ctypes.data_as(C.POINTER(C.c_int64)), band_bin1=_ip(b1), band_bin2=_ip(b2),
+                    band_observed=_dp(bo), band_binless=_dp(bb), sig_cap=tot, sig_bin1=_ip(s1), sig_bin2=_ip(s2), sig_log10=_dp(sv))
+    self.lib._check(self.lib._band_export(self.h, C.byref(p), C.byref(o)), self.h)
+    return {"lam1_sig": sig, "band_bin1": b1, "band_bin2": b2, "band_observed": bo, "band_binless": bb, "nsig": nsig,
+            "sig_bin1": s1[:tot], "sig_bin2": s2[:tot], "sig_log10": sv[:tot]}
+
+
 Handle.cv_score = _cv_score_impl
+Handle.band_export = _band_export_impl
 
 
 def _cts_struct(cts, keep):

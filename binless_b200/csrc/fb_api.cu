@@ -194,6 +194,11 @@ FB_API int fb_cv_score(fb_handle *h, const fb_params *p, int nlam, const double 
     });
 }
 
+FB_API int fb_band_export(fb_handle *h, const fb_band_params *p, fb_band_out *out) {
+    if (!h) { fb::g_last_error = "null handle"; return FB_ERR_ARG; }
+    return guarded(h->m().err, [&] { h->m().band_export(p, out); });   // no solve inside: rank 0 alone on a multi-GPU handle
+}
+
 FB_API int fb_csv_write(const char *path, const char *header, int64_t nrows, int ncols, const double *const *cols, int gzip) {
     if (!path || !header || nrows < 0 || ncols <= 0 || !cols) { fb::g_last_error = "bad argument"; return FB_ERR_ARG; }
     return guarded(fb::g_last_error, [&] {

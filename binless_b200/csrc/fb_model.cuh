@@ -47,6 +47,7 @@ public:
     void eval_cv(const fb_params *p, int nlam, const double *lam2, unsigned group, fb_cv_out *outs);
     void sweep_lambda(const fb_params *p, int nlam, const double *lam2, fb_sweep_out *out);
     void cv_score(const fb_params *p, int nlam, const double *lam2, fb_cv_score_out *out);
+    void band_export(const fb_band_params *p, fb_band_out *out);     // fb_band.cu
 
     std::string err;
     int (*interrupt_cb)(void *) = nullptr;

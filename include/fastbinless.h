@@ -286,6 +286,30 @@ FB_API int FB_NAME(wgfl_diff_bic)(int nbins, const fb_cts *cts, const fb_cts *re
                                   const fb_perf_params *p, const double *phi_ref_init, const double *beta_init,
                                   int warm, fb_gfl_state *gfl, fb_perf_diff_out *out);
 
+/* ---- Output side of chromosome_binless (R/chromosome.R:262-330, signal case) on a fitted or
+ * restored handle: lam1.sig = median(log(signal)) over the cells with distance > far_cutoff, per dataset (lam1_final when
+ * there is none; :270-276), signal := pmax(signal / exp(lam1.sig), 1) (:277), and the triplets R's sparseMatrix() takes:
+ * the band bin2 - bin1 <= maxdiag with `observed` and `binless` (:303-316), and the cells with signal != 1 with
+ * log10(signal) (:318-323). `signal` / `binless` are the data frame columns of fast_binless at the given lam1
+ * (fast_dataframe.cpp:71-76). Bins are 1-based; order is row-major (bin1, then bin2); the sparse arrays are dataset-major.
+ * Call once with the array pointers NULL to learn nband and nsig, then with arrays of that size. */
+typedef struct {
+    double far_cutoff;
+    unsigned maxdiag;
+    double lam1_final;
+    const double *lam1; int n_lam1;
+} fb_band_params;
+typedef struct {
+    double *lam1_sig;                              /* [ndatasets] */
+    int64_t nband;                                 /* out: band cells per dataset */
+    int32_t *band_bin1, *band_bin2;                /* [nband] */
+    double *band_observed, *band_binless;          /* [ndatasets * nband] */
+    int64_t sig_cap;                               /* in: entries the three arrays below can hold */
+    int64_t *nsig;                                 /* [ndatasets] out */
+    int32_t *sig_bin1, *sig_bin2; double *sig_log10;
+} fb_band_out;
+FB_API int FB_NAME(band_export)(fb_handle *h, const fb_band_params *p, fb_band_out *out);
+
 /* Device and pinned-host blocks of destroyed handles are kept in a size-keyed cache (cudaMalloc / cudaFree cost
  * milliseconds per call and fast_binless is called once per locus); this returns them to the driver. */
 FB_API void FB_NAME(release_cached_memory)(void);

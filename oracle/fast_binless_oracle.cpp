@@ -1267,6 +1267,62 @@ void cv_score(Model &m, const fb_params *p, int nlam, const double *lam2v, fb_cv
     out->ms_solver = ms; out->admm_cell_iters = cell_iters;
 }
 
+/* chromosome_binless post-processing and matrix triplets (R/chromosome.R:262-330, signal case), statement by statement on
+ * the data frame columns of fast_binless (fast_dataframe.cpp:62-88) */
+void band_export(Model &m, const fb_band_params *p, fb_band_out *out) {
+    Data &d = m.d;
+    if (!m.has_state) throw std::logic_error("band_export needs a fitted or restored model");
+    const vec lam1 = broadcast(p->lam1, p->n_lam1, d.ndatasets);
+    const vec dc = m.decay_leg.spread(m.dec.get_binned_estimate());
+    vec signal(d.N), binless(d.N);
+    for (unsigned i = 0; i < d.N; ++i) {
+        double l1 = lam1[d.name[i] - 1], lsig = d.beta[i];
+        lsig = (lsig > 0) ? std::max(0., lsig - l1) : std::min(0., lsig + l1);
+        signal[i] = std::exp(lsig); binless[i] = std::exp(dc[i] + lsig);
+    }
+    vec lam1_sig(d.ndatasets);
+    for (unsigned ds = 0; ds < d.ndatasets; ++ds) {     /* mat[distance > far.cutoff, median(log(signal)), by = name] */
+        vec v;
+        for (unsigned c = 0; c < d.ncells; ++c) { const size_t i = (size_t)ds * d.ncells + c; if (d.distance[i] > p->far_cutoff) v.push_back(std::log(signal[i])); }
+        if (v.empty()) { lam1_sig[ds] = p->lam1_final; continue; }
+        std::sort(v.begin(), v.end());
+        const size_t nn = v.size();
+        lam1_sig[ds] = (nn & 1) ? v[nn / 2] : (v[nn / 2 - 1] + v[nn / 2]) / 2;
+        if (std::isnan(lam1_sig[ds])) lam1_sig[ds] = p->lam1_final;
+    }
+    if (out->lam1_sig) std::copy(lam1_sig.begin(), lam1_sig.end(), out->lam1_sig);
+    for (unsigned i = 0; i < d.N; ++i) signal[i] = std::max(signal[i] / std::exp(lam1_sig[d.name[i] - 1]), 1.);   /* :277 */
+    int64_t nband = 0;
+    for (unsigned c = 0; c < d.ncells; ++c) if ((unsigned)(d.bin2[c] - d.bin1[c]) <= p->maxdiag) ++nband;     /* :303 */
+    out->nband = nband;
+    for (unsigned ds = 0; ds < d.ndatasets; ++ds) {
+        int64_t k = 0;
+        for (unsigned c = 0; c < d.ncells; ++c) {
+            const size_t i = (size_t)ds * d.ncells + c;
+            if ((unsigned)(d.bin2[i] - d.bin1[i]) > p->maxdiag) continue;
+            if (ds == 0) { if (out->band_bin1) out->band_bin1[k] = d.bin1[i]; if (out->band_bin2) out->band_bin2[k] = d.bin2[i]; }
+            if (out->band_observed) out->band_observed[(size_t)ds * nband + k] = d.observed[i];
+            if (out->band_binless) out->band_binless[(size_t)ds * nband + k] = binless[i];
+            ++k;
+        }
+    }
+    int64_t total = 0;
+    for (unsigned ds = 0; ds < d.ndatasets; ++ds) {       /* mat[signal != 1] -> log10(signal) (:318-321) */
+        int64_t cnt = 0;
+        for (unsigned c = 0; c < d.ncells; ++c) {
+            const size_t i = (size_t)ds * d.ncells + c;
+            if (signal[i] == 1.) continue;
+            if (out->sig_bin1 && out->sig_bin2 && out->sig_log10) {
+                if (total + cnt >= out->sig_cap) throw ArgError("sig_cap is too small");
+                out->sig_bin1[total + cnt] = d.bin1[i]; out->sig_bin2[total + cnt] = d.bin2[i]; out->sig_log10[total + cnt] = std::log10(signal[i]);
+            }
+            ++cnt;
+        }
+        if (out->nsig) out->nsig[ds] = cnt;
+        total += cnt;
+    }
+}
+
 } // namespace
 
 #include "perf_iteration_oracle.hpp"
@@ -1374,6 +1430,7 @@ FB_API int fbo_eval_cv(fb_handle *h, const fb_params *p, int nlam, const double 
 FB_API int fbo_sweep_lambda(fb_handle *h, const fb_params *p, int nlam, const double *lam2, fb_sweep_out *out) {
     ORACLE_TRY(h, sweep_lambda(h->m, p, nlam, lam2, out))
 }
+FB_API int fbo_band_export(fb_handle *h, const fb_band_params *p, fb_band_out *out) { ORACLE_TRY(h, band_export(h->m, p, out)) }
 FB_API int fbo_cv_score(fb_handle *h, const fb_params *p, int nlam, const double *lam2, fb_cv_score_out *out) {
     ORACLE_TRY(h, cv_score(h->m, p, nlam, lam2, out))
 }

@@ -44,7 +44,10 @@ def test_ctypes_mirror_matches_header_layout(tmp_path):
     """sizeof/offsetof of every struct, computed by the C compiler from the header, equals the ctypes mirror."""
     structs = {"fb_mat": _abi.fb_mat, "fb_params": _abi.fb_params, "fb_mean_state": _abi.fb_mean_state,
                "fb_gam_state": _abi.fb_gam_state, "fb_signal_out": _abi.fb_signal_out, "fb_diff_out": _abi.fb_diff_out,
-               "fb_cv_out": _abi.fb_cv_out, "fb_gfl_state": _abi.fb_gfl_state}
+               "fb_cv_out": _abi.fb_cv_out, "fb_gfl_state": _abi.fb_gfl_state, "fb_cv_score_out": _abi.fb_cv_score_out,
+               "fb_cts": _abi.fb_cts, "fb_perf_meta": _abi.fb_perf_meta, "fb_perf_params": _abi.fb_perf_params,
+               "fb_perf_signal_out": _abi.fb_perf_signal_out, "fb_perf_diff_out": _abi.fb_perf_diff_out,
+               "fb_band_params": _abi.fb_band_params, "fb_band_out": _abi.fb_band_out, "fb_sweep_out": _abi.fb_sweep_out}
     lines = ['#include <stdio.h>', '#include <stddef.h>', f'#include "{HEADER}"', 'int main(void){']
     for name, st in structs.items():
         lines.append(f'printf("{name} %zu\\n", sizeof({name}));')

@@ -345,6 +345,28 @@ def test_cv_score_matches_oracle(gpu_lib, oracle):
     assert rg["admm_cell_iters"] == ro["admm_cell_iters"]
 
 
+@pytest.mark.parametrize("n,D,far,maxdiag", [(64, 2, 150000.0, 10), (129, 1, 1e9, 200), (96, 3, 100000.0, 0)])
+def test_band_export_matches_oracle(gpu_lib, oracle, n, D, far, maxdiag):
+    """fb_band_export (R/chromosome.R:262-330): lam1.sig by an exact device-side median, band triplets,
+    sparse log10-signal triplets: integer columns bit-exact, doubles to 1e-12."""
+    mat = synth(n, D, 5000, 31)
+    with oracle.create(mat, n) as ho:
+        fit = ho.run_signal(0.5, 2.5, 0.05)
+        eo = ho.band_export(far, maxdiag, 0.05, lam1_final=0.07)
+    with gpu_lib.create(mat, n) as hg:
+        hg.restore(fit["log_signal"], fit["biases"], fit["decay"], fit["exposures"])
+        eg = hg.band_export(far, maxdiag, 0.05, lam1_final=0.07)
+        assert hg.kernel_launches() > 0
+    assert np.allclose(eg["lam1_sig"], eo["lam1_sig"], rtol=0, atol=1e-12)
+    if far >= 1e9:
+        assert np.all(eg["lam1_sig"] == 0.07)                 # no far cell: lam1.final
+    for k in ("band_bin1", "band_bin2", "band_observed", "nsig", "sig_bin1", "sig_bin2"):
+        assert np.array_equal(eg[k], eo[k]), k
+    assert np.allclose(eg["band_binless"], eo["band_binless"], rtol=1e-12, atol=0)
+    assert np.allclose(eg["sig_log10"], eo["sig_log10"], rtol=1e-10, atol=1e-13)
+    assert eg["band_bin1"].size == sum(min(maxdiag + 1, n - i) for i in range(n))
+
+
 def _jittered(n, D, seed):
     """a matrix that is NOT a bin_data() layout: distance varies inside a diagonal, positions differ between datasets"""
     mat = synth(n, D, 5000, seed)
