@@ -17,8 +17,8 @@ identical to the oracle's counts) divided by the time of the whole call.
   value : inputs resident in HBM, results left in HBM (fb_run_signal on an existing handle)
   e2e   : the public API with host buffers: fb_create (validation + H2D) + fb_run_signal + every output column D2H
 e2e_pageable : the same call with pageable numpy buffers and every input column passed (what the Rcpp shim supplies)
-c3_sweep, c4_trailblock : the lambda-grid and trail-block configurations of BASELINE.json, sharded over the N ranks
-         (strong scaling), with the bit-identity of a sharded solve against the single-GPU one (see extra_legs)
+c3_sweep, c4_trailblock, c5_chromosome : the lambda-grid, trail-block and whole-chromosome configurations of BASELINE.json,
+         sharded over the N ranks (strong scaling), with the bit-identity of a sharded solve against the single-GPU one
 roofline: the ADMM iteration of the fused-lasso solve (the dominant device work), HBM bound, 104 algorithmic
 bytes per cell per iteration, timed with CUDA events on the solver's stream inside the timed steps.
 """
@@ -343,8 +343,39 @@ def extra_legs(lib, rank, world, local, peak):
     fixed_steps(nb, y4, w4, 2)
     ta, sa, _ = fixed_steps(nb, y4, w4, 2)
     tb, sb, _ = fixed_steps(nb, y4, w4, 12)
+    # ---- C5: chromosome scale end to end (human chr1 at 5 kb: 50 000 bins, 1.25e9 cells), the matrix built in HBM from
+    # cut sites and read pairs (fb_create_binned: bin_data on the device), fast_binless with the lasso on the 2000-wide
+    # band (R/chromosome.R:74,244-246: maxdiag = far.cutoff / base.res, compute_patchnos = F); the ranks share every solve
+    from binless_b200.synth import synth_reads
+    c5 = CONFIGS["C5"]
+    reads = synth_reads(c5["nbins"], 1, c5["res"], c5["seed"], reads_per_dataset=30_000_000)
+    barrier()
+    t0 = time.perf_counter()
+    h5 = lib.create_binned(reads, c5["res"], 1, fetch_mat=False)
+    torch.cuda.synchronize()
+    t_create5 = time.perf_counter() - t0
+    barrier()
+    t0 = time.perf_counter()
+    o5 = h5.run_signal(ALPHA, LAM2, LAM1, columns="none", maxdiag=2000, compute_patchnos=False)
+    barrier()
+    t_call5 = time.perf_counter() - t0
+    d5 = o5["diagnostics"]
+    out["c5_chromosome"] = {"workload": f"C5: fast_binless at {h5.nbins} bins ({h5.ncells} cells, {reads['rd_pos1'].size} read pairs binned on the "
+                                        "device), maxdiag = 2000, compute_patchnos = F, trail blocks over the ranks",
+                            "n_gpus": world, "scaling": "strong", "seconds_create_binned": t_create5, "seconds_fast_binless": t_call5,
+                            "outer_steps": int(d5["nsteps"]), "admm_iters_per_solve": [int(x) for x in d5["solve_iters"]],
+                            "solver_ms": float(d5["ms_solver"]), "Mcell_iter_per_s": d5["admm_cell_iters"] / max(t_call5, 1e-9) / 1e6,
+                            "log_signal_min_is_zero": None}
+    h5.close(); del reads
+    lib.lib.fb_release_cached_memory()
     if world > 1:
         shutdown_comm(lib)
+    # ---- one PROCESS driving several GPUs (fb_gfl_solve_multi: host thread + communicator per device): rank 0, 2 devices
+    if world > 1 and rank == 0:
+        multi = gfl_solve(lib, nchk, yc, wc, 2.5, 1e-12, 16, 0, ngpus=2)
+        out["single_process_2gpu_bit_identical"] = bool(all(np.array_equal(single[k], multi[k]) for k in ("beta", "z", "u", "beta_full"))
+                                                         and single["steps"] == multi["steps"] and single["alpha"] == multi["alpha"])
+    barrier()
     per = (tb - ta) / max(1, sb - sa)
     out["c4_trailblock"] = {"workload": f"C4: one fused-lasso solve, {nb} bins ({nc4} cells), trail blocks over the ranks (fb_comm_init)",
                             "n_gpus": world, "scaling": "strong", "ms_per_admm_iteration": per * 1e3,

@@ -265,7 +265,7 @@ class FastBinlessLib:
         p._keep = (lam2a, lam1a)
         return p
 
-    def create_binned(self, reads, resolution, ndatasets):
+    def create_binned(self, reads, resolution, ndatasets, fetch_mat=True):
         """bin_data() of a CSnorm-like object: ``reads`` holds cut_name, cut_pos (obj@biases) and rd_name, rd_pos1,
         rd_pos2, contact_close / far / up / down (obj@counts). Returns a Handle whose matrix was built by the library."""
         a = {k: _i32(reads[k]) for k in ("cut_name", "cut_pos", "rd_name", "rd_pos1", "rd_pos2", "contact_close",
@@ -275,6 +275,10 @@ class FastBinlessLib:
         h = C.c_void_p(); nb = C.c_int(0)
         self._check(self._create_binned(C.byref(r), C.byref(nb), C.byref(h)), None)
         N = int(self._mat_rows(h))
+        if not fetch_mat:     # chromosome scale: the matrix stays in HBM (what on-device bin_data is for)
+            hd = Handle(self, h, {"distance": np.empty(0)}, nb.value)
+            hd.N = N; hd.ndatasets = N // hd.ncells
+            return hd
         cols = {"distance": np.empty(N)}
         for k in ("name", "bin1", "pos1", "bin2", "pos2", "observed", "nobs"):
             cols[k] = np.empty(N, dtype=np.int32)
