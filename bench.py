@@ -364,8 +364,7 @@ def extra_legs(lib, rank, world, local, peak):
                                         "device), maxdiag = 2000, compute_patchnos = F, trail blocks over the ranks",
                             "n_gpus": world, "scaling": "strong", "seconds_create_binned": t_create5, "seconds_fast_binless": t_call5,
                             "outer_steps": int(d5["nsteps"]), "admm_iters_per_solve": [int(x) for x in d5["solve_iters"]],
-                            "solver_ms": float(d5["ms_solver"]), "Mcell_iter_per_s": d5["admm_cell_iters"] / max(t_call5, 1e-9) / 1e6,
-                            "log_signal_min_is_zero": None}
+                            "solver_ms": float(d5["ms_solver"]), "Mcell_iter_per_s": d5["admm_cell_iters"] / max(t_call5, 1e-9) / 1e6}
     h5.close(); del reads
     lib.lib.fb_release_cached_memory()
     if world > 1:

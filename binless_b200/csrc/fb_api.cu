@@ -77,8 +77,11 @@ private:
         for (size_t r = 0; r < ranks.size(); ++r)
             th.emplace_back([&, r] {     // device buffers go back to the cache of THEIR device
                 cudaSetDevice(ranks[r]->dev);
+                fb::Comm::set_current(&ranks[r]->comm);   // the solvers leave the exchange collectively
                 ranks[r]->m.reset();
+                cudaDeviceSynchronize();
                 ranks[r]->comm.destroy();
+                fb::Comm::set_current(nullptr);
             });
         for (auto &t : th) t.join();
         ranks.clear();

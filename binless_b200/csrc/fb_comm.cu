@@ -91,23 +91,37 @@ void Comm::init(int rank, int world, const void *id128) {
     cudaStreamDestroy(s);
 }
 
+void *Comm::ipc_open(const cudaIpcMemHandle_t &h) {
+    for (auto &e : ipc_) if (std::memcmp(&e.first, &h, sizeof h) == 0) return e.second;
+    void *p = nullptr;
+    if (cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    ipc_.emplace_back(h, p);
+    return p;
+}
+
 void Comm::destroy() {
+    for (auto &e : ipc_) cudaIpcCloseMemHandle(e.second);
+    ipc_.clear();
     if (comm_) { reinterpret_cast<fn_destroy>(fn_[F_DESTROY])(comm_); comm_ = nullptr; }
     rank_ = 0; world_ = 1;
 }
 
-void Comm::group_start() { FB_NCCL(reinterpret_cast<fn_group>(fn_[F_GSTART])()); }
-void Comm::group_end() { FB_NCCL(reinterpret_cast<fn_group>(fn_[F_GEND])()); }
+void Comm::group_start() { need(); FB_NCCL(reinterpret_cast<fn_group>(fn_[F_GSTART])()); }
+void Comm::group_end() { need(); FB_NCCL(reinterpret_cast<fn_group>(fn_[F_GEND])()); }
 void Comm::send(const double *p, size_t n, int peer, cudaStream_t s) {
+    need();
     FB_NCCL(reinterpret_cast<fn_send>(fn_[F_SEND])(p, n, kNcclFloat64, peer, comm_, s));
 }
 void Comm::recv(double *p, size_t n, int peer, cudaStream_t s) {
+    need();
     FB_NCCL(reinterpret_cast<fn_recv>(fn_[F_RECV])(p, n, kNcclFloat64, peer, comm_, s));
 }
 void Comm::allreduce_sum(const double *src, double *dst, size_t n, cudaStream_t s) {
+    need();
     FB_NCCL(reinterpret_cast<fn_allreduce>(fn_[F_ALLREDUCE])(src, dst, n, kNcclFloat64, kNcclSum, comm_, s));
 }
 void Comm::bcast(double *p, size_t n, int root, cudaStream_t s) {
+    need();
     FB_NCCL(reinterpret_cast<fn_bcast>(fn_[F_BCAST])(p, p, n, kNcclFloat64, root, comm_, s));
 }
 

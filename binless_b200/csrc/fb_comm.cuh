@@ -40,7 +40,12 @@ public:
     void recv(double *p, size_t n, int peer, cudaStream_t s);
     void allreduce_sum(const double *src, double *dst, size_t n, cudaStream_t s);
     void bcast(double *p, size_t n, int root, cudaStream_t s);
+    // CUDA IPC mapping of a peer's allocation, kept for the life of the communicator (opening one costs tens of
+    // milliseconds; the solver of every solve asks for the same blocks again); nullptr when it cannot be opened
+    void *ipc_open(const cudaIpcMemHandle_t &h);
 private:
+    void need() const { if (!comm_) throw CommError("no communicator (fb_comm_init has not been called on this thread)"); }
+    std::vector<std::pair<cudaIpcMemHandle_t, void *>> ipc_;
     void load();
     void *lib_ = nullptr, *comm_ = nullptr;
     int rank_ = 0, world_ = 1;

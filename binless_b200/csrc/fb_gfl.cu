@@ -19,11 +19,14 @@
 #include "fb_comm.cuh"
 #include "fb_taut.cuh"
 #include "fb_prox_aset.cuh"
+#include "fb_ctl.cuh"
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <vector>
+#include <cstring>
+#include <unistd.h>
 
 namespace fb {
 
@@ -281,8 +284,9 @@ __global__ void __launch_bounds__(64 * (GS ? PROX_GS_TEAMS : PROX_MAX_TEAMS), 1)
 k_prox(Grid g, GflCtl *__restrict__ ctl, const double *__restrict__ beta, const double *__restrict__ betaT,
        double *__restrict__ zr, double *__restrict__ ur, double *__restrict__ zc, double *__restrict__ uc,
        double *__restrict__ partials, int stride, int rlen, long long *__restrict__ trace,
-       const int *__restrict__ list, const int nlist, double *__restrict__ gscratch) {
+       const int *__restrict__ list, const int nlist, double *__restrict__ gscratch, const GflFold fold) {
     if (ctl->done || ctl->prox_sel) return;   // prox_sel: this iteration belongs to k_prox_aset
+    __shared__ int s_last;
     extern __shared__ double smem[];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int team = wid >> 1, side = wid & 1, bar = 1 + team;
@@ -443,6 +447,11 @@ k_prox(Grid g, GflCtl *__restrict__ ctl, const double *__restrict__ beta, const 
         team_sync(bar); // both warps are done with S; the next chain is published
         qi = ti[8];
     }
+    // the last CTA to finish ends the iteration (residual norms, convergence, penalty): no k_ctl launch
+    if (fold.on) {
+        __syncthreads();     // every team of this CTA is done with the shared memory
+        ctl_fold(ctl, fold, partials, &s_last, smem);
+    }
 }
 
 // --------------------------------------------------------------------------
@@ -482,6 +491,52 @@ k_exchange(Grid g, const GflCtl *__restrict__ ctl, const ShardRegion *__restrict
     }
 }
 
+// The same terms stored straight into the peers' arrays (same layout on every rank => same index): grid (lines, peers)
+template <int DIR>
+__global__ void __launch_bounds__(256)
+k_push(Grid g, const GflCtl *__restrict__ ctl, const ShardRegion *__restrict__ regs, const double *__restrict__ z,
+       const double *__restrict__ u, double *const *__restrict__ peer) {
+    if (ctl->idle) return;
+    const ShardRegion r = regs[2 * blockIdx.y + DIR];
+    double *__restrict__ dst = peer[blockIdx.y];
+    const int mode = ctl->rescale;
+    const double inflate = ctl->inflate;
+    for (int line = r.l0 + blockIdx.x; line < r.l1; line += gridDim.x) {
+        int lo, hi; int64_t base;
+        if (DIR == 0) {
+            lo = max(r.x0, line); hi = min(r.x1, line + g.row_len(line));
+            base = g.rm_row_start(line) + (lo - line);
+        } else {
+            const int f = g.col_first_row(line);
+            lo = max(r.x0, f); hi = min(r.x1, line + 1);
+            base = g.cm_col_start(line) + (lo - f);
+        }
+        for (int x = threadIdx.x; x < hi - lo; x += blockDim.x) {
+            double uu = u[base + x];
+            if (mode == 1) uu = uu / inflate; else if (mode == 2) uu = uu * inflate;
+            dst[base + x] = z[base + x] - uu;
+        }
+    }
+}
+// the duals of the cells whose chains another rank owns are zero here (their z holds z - u of the owner)
+template <int DIR>
+__global__ void __launch_bounds__(256)
+k_zero_remote_u(Grid g, const ShardRegion *__restrict__ regs, double *__restrict__ u) {
+    const ShardRegion r = regs[2 * blockIdx.y + DIR];
+    for (int line = r.l0 + blockIdx.x; line < r.l1; line += gridDim.x) {
+        int lo, hi; int64_t base;
+        if (DIR == 0) {
+            lo = max(r.x0, line); hi = min(r.x1, line + g.row_len(line));
+            base = g.rm_row_start(line) + (lo - line);
+        } else {
+            const int f = g.col_first_row(line);
+            lo = max(r.x0, f); hi = min(r.x1, line + 1);
+            base = g.cm_col_start(line) + (lo - f);
+        }
+        for (int x = threadIdx.x; x < hi - lo; x += blockDim.x) u[base + x] = 0.0;
+    }
+}
+
 // --------------------------------------------------------------------------
 // residual norms, convergence, varying penalty (gfl_graph_fl.c:159-181)
 // --------------------------------------------------------------------------
@@ -489,33 +544,8 @@ template <bool GRAPH>
 __global__ void __launch_bounds__(CTL_THREADS)
 k_ctl(GflCtl *ctl, const double *__restrict__ partials, int npart, int64_t ncells, int64_t nz, cudaGraphConditionalHandle cond) {
     if (ctl->done) { if (threadIdx.x == 0) { ctl->idle = 1; if (GRAPH) cudaGraphSetConditional(cond, 0); } return; }
-    __shared__ double s_p[CTL_THREADS], s_d[CTL_THREADS];
-    double p = 0.0, d = 0.0;
-    for (int k = threadIdx.x; k < npart; k += CTL_THREADS) { p += partials[2 * k]; d += partials[2 * k + 1]; }
-    s_p[threadIdx.x] = p; s_d[threadIdx.x] = d;
-    __syncthreads();
-    for (int o = CTL_THREADS / 2; o > 0; o >>= 1) {
-        if ((int)threadIdx.x < o) { s_p[threadIdx.x] += s_p[threadIdx.x + o]; s_d[threadIdx.x] += s_d[threadIdx.x + o]; }
-        __syncthreads();
-    }
-    if (threadIdx.x == 0) {
-        const double rp = sqrt(s_p[0] / (double)ncells);
-        const double rd = sqrt(s_d[0] / (double)nz);
-        const double cur = rp > rd ? rp : rd;
-        ctl->presnorm = rp; ctl->dresnorm = rd;
-        int step = ctl->step;
-        int rescale = 0;
-        if (step % 50 == 0 && rp > 10 * rd) { ctl->alpha *= ctl->inflate; rescale = 1; }
-        else if (step % 50 == 0 && rd > 10 * rp) { ctl->alpha /= ctl->inflate; rescale = 2; }
-        ctl->rescale = rescale;
-        ++step;
-        ctl->step = step;
-        ctl->next_chain = 0; // work queue of the next k_prox launch
-        ctl->prox_sel = (ctl->aset_from >= 0 && step >= ctl->aset_from) ? 1 : 0;
-        const int done = !(step < ctl->maxsteps && cur > ctl->converge);
-        ctl->done = done;
-        if (GRAPH) cudaGraphSetConditional(cond, done ? 0u : 1u);   // the WHILE node runs the next iteration or stops
-    }
+    __shared__ double sm[2 * CTL_VT];
+    ctl_tail(ctl, partials, npart, ncells, nz, cond, GRAPH, sm);
 }
 
 // applies a pending dual rescale after the last iteration of a solve
@@ -611,6 +641,7 @@ GflSolver::GflSolver(int nbins, unsigned maxdiag, cudaStream_t stream) : nbins_(
         prox_warps_ = prox_gs_ ? PROX_GS_TEAMS : std::min<int64_t>(PROX_MAX_TEAMS, fit);
         prox_warps_ = std::min(prox_warps_, std::max(1, (g_.nchains() + n_sm_ - 1) / n_sm_));
         prox_smem_ = prox_gs_ ? ((size_t)prox_rlen_ + 8 * prox_warps_ + 8) * 8 : ((size_t)prox_warps_ * prox_stride_ + prox_rlen_) * 8;
+        prox_smem_ = std::max(prox_smem_, (size_t)2 * CTL_VT * sizeof(double));   // the last CTA reduces the residual sums there (fb_ctl.cuh)
         const void *fn = prox_long_ ? (const void *)k_prox<true, true> : prox_gs_ ? (const void *)k_prox<false, true> : (const void *)k_prox<false, false>;
         FB_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)prox_smem_));
         prox_grid_ = std::min(n_sm_, (g_.nchains() + prox_warps_ - 1) / prox_warps_);
@@ -629,6 +660,10 @@ GflSolver::GflSolver(int nbins, unsigned maxdiag, cudaStream_t stream) : nbins_(
         use_aset_ = aset_->usable;
         if (const char *f = std::getenv("FB_ASET_FROM")) aset_from_ = std::max(1, std::atoi(f));
     }
+    // FB_CTL_FOLD=1: the last CTA of the chain-prox kernel ends the iteration itself instead of a k_ctl launch. Measured on
+    // B200 at C2: 237 us per iteration against 231 with the separate launch (the tail sits on the critical path of the
+    // slowest CTA, the 1024-thread k_ctl overlaps the drain of the prox kernel), so it is off by default.
+    fold_ctl_ = !sharded_ && std::getenv("FB_CTL_FOLD") && std::atoi(std::getenv("FB_CTL_FOLD")) != 0;
     // the polling loop stays for the sharded solve (collectives between the kernels) and the trace aid
     use_graph_ = !sharded_ && !trace_.p && st_ != nullptr && !std::getenv("FB_NO_GRAPH");
     reset();
@@ -701,7 +736,73 @@ void GflSolver::setup_shard() {
     send_buf_.zero(st_); recv_buf_.zero(st_);
     partials_.zero(st_);   // chains of other ranks contribute exact zeros to the all-reduce
     partials_all_.alloc(partials_.n);
+    setup_p2p();
 }
+
+// Exchange of the array addresses: per rank {IPC handle of zr, of zc, raw pointers, pid, device}, broadcast from every
+// rank in turn. A peer in this process is written through its raw pointer (peer access enabled), a peer in another
+// process through the opened IPC handle. Any failure anywhere (no IPC in this container, no peer access) makes EVERY rank
+// fall back to the packed ncclSend / ncclRecv exchange: the decision is all-reduced.
+void GflSolver::setup_p2p() {
+    Comm &cm = Comm::get();
+    struct Info { cudaIpcMemHandle_t hr, hc; unsigned long long pr, pc; long long pid, dev; };
+    static_assert(sizeof(Info) % sizeof(double) == 0, "Info is sent as doubles");
+    constexpr int ND = sizeof(Info) / sizeof(double);
+    const char *env = std::getenv("FB_SHARD_P2P");
+    bool ok = !(env && std::atoi(env) == 0);
+    std::vector<Info> info(world_);
+    std::memset(info.data(), 0, info.size() * sizeof(Info));
+    Info &me = info[rank_];
+    int dev = 0; cudaGetDevice(&dev);
+    me.pr = (unsigned long long)zr_.p; me.pc = (unsigned long long)zc_.p; me.pid = (long long)getpid(); me.dev = dev;
+    if (ok && (cudaIpcGetMemHandle(&me.hr, zr_.p) != cudaSuccess || cudaIpcGetMemHandle(&me.hc, zc_.p) != cudaSuccess)) { cudaGetLastError(); ok = false; }
+    DevBuf<double> buf((size_t)ND * world_);
+    FB_CUDA(cudaMemcpyAsync(buf.p + (size_t)ND * rank_, &me, sizeof(Info), cudaMemcpyHostToDevice, st_));
+    cm.group_start();
+    for (int p = 0; p < world_; ++p) cm.bcast(buf.p + (size_t)ND * p, ND, p, st_);
+    cm.group_end();
+    FB_CUDA(cudaMemcpyAsync(info.data(), buf.p, info.size() * sizeof(Info), cudaMemcpyDeviceToHost, st_));
+    FB_CUDA(cudaStreamSynchronize(st_));
+    std::vector<double *> pr, pc;
+    for (int p = 0; p < world_ && ok; ++p) {
+        if (p == rank_) continue;
+        double *r = nullptr, *c = nullptr;
+        if (info[p].pid == me.pid) {     // same process (fb_create_multi): one address space
+            int can = 0;
+            if (cudaDeviceCanAccessPeer(&can, dev, (int)info[p].dev) != cudaSuccess || !can) { cudaGetLastError(); ok = false; break; }
+            const cudaError_t e = cudaDeviceEnablePeerAccess((int)info[p].dev, 0);
+            if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) { cudaGetLastError(); ok = false; break; }
+            cudaGetLastError();
+            r = (double *)info[p].pr; c = (double *)info[p].pc;
+        } else {
+            void *a = cm.ipc_open(info[p].hr), *b = a ? cm.ipc_open(info[p].hc) : nullptr;   // kept open by the communicator
+            if (!a || !b) { ok = false; break; }
+            p2p_ipc_ = true;
+            r = (double *)a; c = (double *)b;
+        }
+        pr.push_back(r); pc.push_back(c);
+    }
+    // agree: the sum of the failure flags over the ranks
+    bar_.alloc(4);
+    const double fail[2] = {ok ? 0.0 : 1.0, 0.0};
+    FB_CUDA(cudaMemcpyAsync(bar_.p, fail, sizeof fail, cudaMemcpyHostToDevice, st_));
+    cm.allreduce_sum(bar_.p, bar_.p + 2, 2, st_);
+    double tot[2] = {0, 0};
+    FB_CUDA(cudaMemcpyAsync(tot, bar_.p + 2, sizeof tot, cudaMemcpyDeviceToHost, st_));
+    FB_CUDA(cudaStreamSynchronize(st_));
+    if ((std::getenv("FB_SHARD_VERBOSE") || shard_timing_) && rank_ == 0)
+        std::fprintf(stderr, "[fb shard] exchange of the crossing terms: %s\n",
+                     tot[0] != 0.0 ? "packed ncclSend / ncclRecv" : (p2p_ipc_ ? "peer stores (CUDA IPC)" : "peer stores (same process)"));
+    if (tot[0] != 0.0) { teardown_p2p(); p2p_ = false; return; }
+    peer_zr_.alloc(std::max<size_t>(1, pr.size())); peer_zc_.alloc(std::max<size_t>(1, pc.size()));
+    if (!pr.empty()) {
+        FB_CUDA(cudaMemcpy(peer_zr_.p, pr.data(), pr.size() * sizeof(double *), cudaMemcpyHostToDevice));
+        FB_CUDA(cudaMemcpy(peer_zc_.p, pc.data(), pc.size() * sizeof(double *), cudaMemcpyHostToDevice));
+    }
+    p2p_ = true;
+}
+
+void GflSolver::teardown_p2p() {}   // the IPC mappings belong to the communicator (Comm::ipc_open)
 
 void GflSolver::tmark(int k) {
     if (!shard_timing_) return;
@@ -718,6 +819,25 @@ void GflSolver::tflush() { // after a stream synchronisation: add the phases of 
 void GflSolver::exchange(bool zero_u) {
     Comm &cm = Comm::get();
     dim3 grid((unsigned)std::min(max_lines_, 4096), (unsigned)(world_ - 1));
+    if (p2p_) {
+        if (zero_u) {
+            // start of a solve: no peer may store into this rank's arrays before its own resets / state imports (queued
+            // on this stream) are done, so everybody waits for everybody first
+            cm.allreduce_sum(bar_.p, bar_.p + 2, 1, st_);
+            k_zero_remote_u<0><<<grid, 256, 0, st_>>>(g_, recv_regs_.p, ur_.p);
+            k_zero_remote_u<1><<<grid, 256, 0, st_>>>(g_, recv_regs_.p, uc_.p);
+            kernel_launches += 2;
+        }
+        tmark(5);
+        k_push<0><<<grid, 256, 0, st_>>>(g_, ctl_.p, send_regs_.p, zr_.p, ur_.p, peer_zr_.p);
+        k_push<1><<<grid, 256, 0, st_>>>(g_, ctl_.p, send_regs_.p, zc_.p, uc_.p, peer_zc_.p);
+        kernel_launches += 2;
+        tmark(6);
+        // every rank's stores precede its contribution: when the sum arrives, all the terms this rank reads next have landed
+        cm.allreduce_sum(bar_.p, bar_.p + 2, 1, st_);
+        tmark(7);
+        return;
+    }
     k_exchange<0, true><<<grid, 256, 0, st_>>>(g_, ctl_.p, send_regs_.p, send_lineoff_.p, zr_.p, ur_.p, send_buf_.p, 0);
     k_exchange<1, true><<<grid, 256, 0, st_>>>(g_, ctl_.p, send_regs_.p, send_lineoff_.p, zc_.p, uc_.p, send_buf_.p, 0);
     tmark(5);
@@ -757,8 +877,15 @@ void GflSolver::allgather_cols(double *a) {
 
 GflSolver::~GflSolver() {
     cudaStreamSynchronize(st_); // buffers go back to the block cache only when nothing uses them any more
+    if (sharded_ && p2p_) {
+        // no peer may still be storing into these arrays when they go back to the cache (and no handle stays open)
+        try { Comm::get().allreduce_sum(bar_.p, bar_.p + 2, 1, st_); cudaStreamSynchronize(st_); } catch (...) {}
+        teardown_p2p();
+    }
     if (shard_timing_ && tcount_) {
-        static const char *nm[7] = {"k_beta", "k_prox", "allreduce", "k_ctl", "pack", "send/recv", "unpack"};
+        static const char *nm_nccl[7] = {"k_beta", "k_prox", "allreduce", "k_ctl", "pack", "send/recv", "unpack"};
+        static const char *nm_p2p[7] = {"k_beta", "k_prox", "allreduce", "k_ctl", "-", "push (peer stores)", "barrier"};
+        const char **nm = p2p_ ? nm_p2p : nm_nccl;
         std::fprintf(stderr, "[fb shard timing] rank %d n=%d, mean over %d sampled iterations (ms):", rank_, g_.n, tcount_);
         for (int k = 0; k < 7; ++k) std::fprintf(stderr, " %s %.3f", nm[k], tacc_[k] / tcount_);
         std::fprintf(stderr, "\n");
@@ -786,10 +913,15 @@ void GflSolver::launch_iteration(const double *y, const double *w, bool in_graph
     const int *list = sharded_ ? chain_list_.p : nullptr;
     // both chain-prox kernels are launched; the one ctl->prox_sel does not name returns at once (k_ctl picks per step:
     // the taut-string search is faster while the string has few knots, the parallel active set afterwards)
-    if (use_aset_) aset_prox_launch(*aset_, ctl_.p, beta_.p, betaT_.p, zr_.p, ur_.p, zc_.p, uc_.p, partials_.p, st_);
+    // not sharded: the last CTA of the chain-prox kernel ends the iteration itself (no k_ctl launch); sharded: the
+    // partial sums are all-reduced first, k_ctl follows
+    GflFold fold{};
+    fold.on = fold_ctl_ ? 1 : 0; fold.graph = in_graph ? 1 : 0; fold.npart = n_partials_;
+    fold.ncells = g_.ncells; fold.nz = 2 * g_.ncells - 2; fold.cond = cond_;
+    if (use_aset_) aset_prox_launch(*aset_, ctl_.p, beta_.p, betaT_.p, zr_.p, ur_.p, zc_.p, uc_.p, partials_.p, fold, st_);
 #define FB_PROX_LAUNCH(LONG_, GS_)                                                                                              \
     k_prox<LONG_, GS_><<<prox_grid_, 64 * prox_warps_, prox_smem_, st_>>>(g_, ctl_.p, beta_.p, betaT_.p, zr_.p, ur_.p, zc_.p, uc_.p,  \
-                                                                         partials_.p, prox_stride_, prox_rlen_, trace_.p, list, n_list_, gscratch_.p)
+                                                                         partials_.p, prox_stride_, prox_rlen_, trace_.p, list, n_list_, gscratch_.p, fold)
     if (prox_long_) FB_PROX_LAUNCH(true, true);
     else if (prox_gs_) FB_PROX_LAUNCH(false, true);
     else FB_PROX_LAUNCH(false, false);
@@ -800,6 +932,7 @@ void GflSolver::launch_iteration(const double *y, const double *w, bool in_graph
     if (sharded_) Comm::get().allreduce_sum(partials_.p, partials_all_.p, 2 * (size_t)n_partials_, st_);
     tmark(3);
     const double *parts = sharded_ ? partials_all_.p : partials_.p;
+    if (fold.on) { tmark(4); return; }
     if (in_graph) k_ctl<true><<<1, CTL_THREADS, 0, st_>>>(ctl_.p, parts, n_partials_, g_.ncells, 2 * g_.ncells - 2, cond_);
     else k_ctl<false><<<1, CTL_THREADS, 0, st_>>>(ctl_.p, parts, n_partials_, g_.ncells, 2 * g_.ncells - 2, cond_);
     tmark(4);
@@ -809,7 +942,7 @@ void GflSolver::launch_iteration(const double *y, const double *w, bool in_graph
 void GflSolver::iteration(const double *y, const double *w, int parity) {
     (void)parity;
     launch_iteration(y, w, false);
-    kernel_launches += use_aset_ ? 4 : 3;
+    kernel_launches += (use_aset_ ? 4 : 3) - (fold_ctl_ ? 1 : 0);
 }
 
 // One iteration captured into the body of a WHILE conditional node (CUDA >= 12.4). The kernels read y / w from the
@@ -846,7 +979,7 @@ int GflSolver::optimize(const double *d_y_tri, const double *d_w_tri, double lam
     c.alpha = alpha; c.lam = lam2; c.converge = converge; c.inflate = inflate;
     c.presnorm = c.dresnorm = 0; c.step = 1; c.maxsteps = ninner_max;
     c.done = !(c.step < c.maxsteps && (converge + 1) > converge);
-    c.rescale = 0; c.next_chain = 0; c.idle = 0;
+    c.rescale = 0; c.next_chain = 0; c.idle = 0; c.ctas_done = 0;
     c.aset_from = use_aset_ ? (cold_ ? aset_from_ : 0) : -1;
     c.prox_sel = (c.aset_from >= 0 && c.step >= c.aset_from) ? 1 : 0;
     c.y = y; c.w = w;
@@ -861,7 +994,7 @@ int GflSolver::optimize(const double *d_y_tri, const double *d_w_tri, double lam
         FB_CUDA(cudaMemcpyAsync(h_ctl_, ctl_.p, sizeof(GflCtl), cudaMemcpyDeviceToHost, st_));
         FB_CUDA(cudaStreamSynchronize(st_));
         if (!h_ctl_->done) throw CudaError("the captured ADMM loop ended without setting done");
-        kernel_launches += (use_aset_ ? 4 : 3) * (int64_t)(h_ctl_->step - 1);
+        kernel_launches += ((use_aset_ ? 4 : 3) - (fold_ctl_ ? 1 : 0)) * (int64_t)(h_ctl_->step - 1);
         done = true;
     }
     while (!done) {

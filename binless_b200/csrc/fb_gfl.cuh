@@ -62,6 +62,14 @@ struct GflCtl {
     int prox_sel;     // chain prox of the NEXT iteration: 0 taut-string team kernel k_prox, 1 parallel active set k_prox_aset
     int aset_from;    // first step (1-based) that uses k_prox_aset; -1 never
     const double *y, *w;   // inputs of the running solve (the kernels of the captured iteration read them from here)
+    int ctas_done;    // CTAs of the running chain-prox kernel that have finished (the last one ends the iteration, fb_ctl.cuh)
+};
+
+// What the last CTA of a chain-prox kernel needs to end the iteration itself (on = 0: a separate k_ctl launch follows)
+struct GflFold {
+    int on, graph, npart;
+    int64_t ncells, nz;
+    cudaGraphConditionalHandle cond;
 };
 
 // Trail-block sharding (one process per GPU): the cells {line in [l0,l1), x in [x0,x1)} of the
@@ -129,6 +137,16 @@ private:
     void tflush();
     void setup_shard();
     void exchange(bool zero_u);
+    // Direct exchange over peer memory (NVLink): every rank's z arrays have the same layout, so the owner of a chain
+    // stores z - u of a crossing cell straight into the peer's array at the same index (one kernel per direction, no
+    // pack / ncclSend / ncclRecv / unpack); peers in other processes are reached through CUDA IPC handles, peers in this
+    // process (fb_create_multi) through plain pointers. One scalar all-reduce after the stores is the barrier.
+    bool p2p_ = false;
+    DevBuf<double *> peer_zr_, peer_zc_;     // per exchange partner (region order): its zr / zc
+    bool p2p_ipc_ = false;
+    DevBuf<double> bar_;
+    void setup_p2p();
+    void teardown_p2p();
     void allgather_rows(double *rm_array);
     void allgather_cols(double *cm_array);
     DevBuf<GflCtl> ctl_;
@@ -150,6 +168,7 @@ private:
     cudaEvent_t ev0_, ev1_;
     // the whole ADMM loop as ONE graph launch: a WHILE conditional node whose body is one iteration, the condition
     // set on the device by k_ctl (no host polling, no launches queued past convergence)
+    bool fold_ctl_ = false;            // FB_CTL_FOLD: see the constructor
     bool use_graph_ = false;
     cudaGraph_t graph_ = nullptr;
     cudaGraphExec_t graph_exec_ = nullptr;

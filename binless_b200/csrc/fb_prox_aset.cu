@@ -28,9 +28,11 @@
 // or which rank owns them.
 #include "fb_prox_aset.cuh"
 #include "fb_prox_aset_passes.cuh"
+#include "fb_ctl.cuh"
 #include <algorithm>
 #include <cstdio>
 #include <cstdlib>
+#include <cstddef>
 
 namespace fb {
 
@@ -80,7 +82,7 @@ k_prox_aset(GflCtl *__restrict__ ctl, const AsChain *__restrict__ chains, const 
             const AsWord *__restrict__ words, const int nbatches, const int maxpass,
             const double *__restrict__ beta, const double *__restrict__ betaT,
             double *__restrict__ zr, double *__restrict__ ur, double *__restrict__ zc, double *__restrict__ uc,
-            double *__restrict__ partials, unsigned long long *__restrict__ stats) {
+            double *__restrict__ partials, unsigned long long *__restrict__ stats, const GflFold fold) {
     if (ctl->done || !ctl->prox_sel) return;   // !prox_sel: this iteration belongs to the team kernel k_prox
     extern __shared__ __align__(16) unsigned char smem_raw[];
     SmT<CAP> &s = *reinterpret_cast<SmT<CAP> *>(smem_raw);
@@ -316,6 +318,10 @@ k_prox_aset(GflCtl *__restrict__ ctl, const AsChain *__restrict__ chains, const 
         bi = s.ci[C_BATCH];
         __syncthreads();
     }
+    // the last CTA to finish ends the iteration (residual norms, convergence, penalty): no k_ctl launch. S and SLP are
+    // adjacent arrays of CAP >= 1024 doubles each: room for the 2 x 1024 sums of the reduction
+    static_assert(offsetof(SmT<CAP>, SLP) == sizeof(double) * CAP && CAP >= CTL_VT, "S and SLP hold the reduction");
+    ctl_fold(ctl, fold, partials, &s.ci[1], &s.S[0]);
 }
 
 } // namespace
@@ -412,12 +418,12 @@ void aset_plan_build(AsetPlan &plan, const Grid &g, int r0, int r1, int c0, int 
 }
 
 void aset_prox_launch(const AsetPlan &plan, GflCtl *ctl, const double *beta, const double *betaT, double *zr, double *ur,
-                      double *zc, double *uc, double *partials, cudaStream_t st) {
+                      double *zc, double *uc, double *partials, const GflFold &fold, cudaStream_t st) {
     if (!plan.nbatches) return;
     if (plan.stats.p) FB_CUDA(cudaMemsetAsync(plan.stats.p, 0, 8 * sizeof(unsigned long long), st));
 #define FB_ASET_LAUNCH(CAP_)                                                                                                   \
     case CAP_: k_prox_aset<CAP_><<<plan.grid, AS_NT, plan.smem, st>>>(ctl, plan.chains.p, plan.batches.p, plan.words.p, plan.nbatches, \
-                                                                     plan.maxpass, beta, betaT, zr, ur, zc, uc, partials, plan.stats.p); break;
+                                                                     plan.maxpass, beta, betaT, zr, ur, zc, uc, partials, plan.stats.p, fold); break;
     switch (plan.cap) {
         FB_ASET_LAUNCH(1024) FB_ASET_LAUNCH(2048) FB_ASET_LAUNCH(2432) FB_ASET_LAUNCH(3072) FB_ASET_LAUNCH(4096) FB_ASET_LAUNCH(5632)
         default: throw StateError("k_prox_aset: no kernel for this capacity");

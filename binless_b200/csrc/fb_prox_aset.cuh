@@ -39,6 +39,6 @@ struct AsetPlan {
 void aset_plan_build(AsetPlan &plan, const Grid &g, int r0, int r1, int c0, int c1, int n_sm);
 
 void aset_prox_launch(const AsetPlan &plan, GflCtl *ctl, const double *beta, const double *betaT, double *zr, double *ur,
-                      double *zc, double *uc, double *partials, cudaStream_t st);
+                      double *zc, double *uc, double *partials, const GflFold &fold, cudaStream_t st);
 
 } // namespace fb
