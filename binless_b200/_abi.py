@@ -118,7 +118,7 @@ ENTRY_POINTS = ["create", "destroy", "last_error", "run_signal", "restore", "run
                 "comm_unique_id", "comm_init", "comm_destroy", "comm_rank", "comm_world", "shard_plan",
                 "create_binned", "get_mat", "mat_rows", "cv_score", "csv_write",
                 "wgfl_signal_bic", "wgfl_diff_bic", "create_multi", "handle_ngpus", "gfl_solve_multi",
-                "band_export"]
+                "band_export", "gfl_last_solve_ms"]
 
 
 def _dp(a):
@@ -206,6 +206,7 @@ class FastBinlessLib:
         self._gfl_solve_multi.restype = C.c_int
         self._band_export = f("band_export")
         self._band_export.argtypes = [C.c_void_p, C.POINTER(fb_band_params), C.POINTER(fb_band_out)]; self._band_export.restype = C.c_int
+        self._gfl_last_solve_ms = f("gfl_last_solve_ms"); self._gfl_last_solve_ms.argtypes = []; self._gfl_last_solve_ms.restype = C.c_double
         self._kernel_launches = f("kernel_launches")
         self._kernel_launches.argtypes = [C.c_void_p]; self._kernel_launches.restype = C.c_int64
         self._gfl_solve = f("gfl_solve")

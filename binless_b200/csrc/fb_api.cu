@@ -5,6 +5,7 @@
 #include "fb_comm.cuh"
 #include "fb_csv.hpp"
 #include "fb_perf.cuh"
+#include <atomic>
 #include <exception>
 #include <memory>
 #include <string>
@@ -233,6 +234,7 @@ FB_API void fb_release_cached_memory(void) {
 
 FB_API int64_t fb_kernel_launches(const fb_handle *h) { return h ? h->m().kernel_launches : 0; }
 
+namespace { thread_local double tl_last_solve_ms = 0.0; std::atomic<double> g_multi_solve_ms{0.0}; }
 namespace {
 // FusedLassoGaussianEstimator<GFLLibrary>::optimize on the current device (and communicator)
 void gfl_solve_body(int nbins, unsigned maxdiag, const double *y, const double *w, double lam2, double converge, int maxsteps,
@@ -249,6 +251,8 @@ void gfl_solve_body(int nbins, unsigned maxdiag, const double *y, const double *
     dy.upload(y, nc); dw.upload(w, nc);
     if (warm) { s.alpha = st->alpha; s.import_state(st->beta, st->z, st->u); }
     s.optimize(dy.p, dw.p, lam2, converge);
+    tl_last_solve_ms = s.ms_last;
+    if (fb::Comm::get().rank() == 0) g_multi_solve_ms.store(s.ms_last);
     st->alpha = s.alpha; st->steps = s.last_steps;
     s.export_state(st->beta, st->z, st->u);
     if (beta_full) {
@@ -312,8 +316,11 @@ FB_API int fb_gfl_solve_multi(int ngpus, int nbins, unsigned maxdiag, const doub
             });
         for (auto &t : th) t.join();
         for (auto &e : ex) if (e) std::rethrow_exception(e);
+        tl_last_solve_ms = g_multi_solve_ms.load();      // rank 0's thread measured it
     });
 }
+
+FB_API double fb_gfl_last_solve_ms(void) { return tl_last_solve_ms; }
 
 // ---- one process per GPU: trail-block sharding of the fused-lasso solve over the ranks of one NCCL communicator ----
 FB_API int fb_comm_unique_id(void *id128) {

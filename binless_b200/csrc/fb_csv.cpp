@@ -11,6 +11,7 @@
 #include <zlib.h>
 #include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <future>
 #include <string>
@@ -49,7 +50,8 @@ bool write_csv_gz(const char *path, const char *header, int64_t nrows, int ncols
     FILE *f = std::fopen(path, "wb");
     if (!f) { std::printf("Exception creating csv file: cannot open %s\n", path); return false; } // the reference only reports it
     bool ok = true;
-    const int nthr = (int)std::min(16u, std::max(1u, std::thread::hardware_concurrency()));
+    int nthr = (int)std::min(16u, std::max(1u, std::thread::hardware_concurrency()));
+    if (const char *e = std::getenv("FB_HOST_THREADS")) nthr = std::max(1, std::min(64, std::atoi(e)));
     const int64_t slab = int64_t(1) << 20;      // rows per slab: a few tens of MB of text in flight
     uLong crc = crc32(0L, Z_NULL, 0);
     uint64_t total = 0;

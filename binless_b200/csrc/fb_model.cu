@@ -99,9 +99,18 @@ size_t stage_min_bytes() {
     return v;
 }
 
+// Host threads of this process for validation / staging copies: FB_HOST_THREADS, else the cores divided by the ranks that
+// share the machine (LOCAL_WORLD_SIZE, set by torchrun / mpirun wrappers): eight ranks with sixteen threads each on a
+// sixteen-core host was what made the end-to-end time collapse at 8 GPUs.
 int host_threads() {
-    unsigned h = std::thread::hardware_concurrency();
-    return (int)std::min(16u, std::max(1u, h));
+    static const int v = [] {
+        const unsigned h = std::max(1u, std::thread::hardware_concurrency());
+        if (const char *e = std::getenv("FB_HOST_THREADS")) return std::max(1, std::min(64, std::atoi(e)));
+        int local = 1;
+        if (const char *e = std::getenv("LOCAL_WORLD_SIZE")) local = std::max(1, std::atoi(e));
+        return (int)std::max(1u, std::min(16u, h / (unsigned)local));
+    }();
+    return v;
 }
 
 } // namespace

@@ -43,3 +43,27 @@ def init_comm(lib=None):
 def shutdown_comm(lib=None):
     from . import cuda_lib
     (lib or cuda_lib()).comm_destroy()
+
+
+def bind_to_gpu_numa_node(device_index: int):
+    """Pin this process (and the library's staging threads, which inherit the mask) to the CPUs of the NUMA node the GPU
+    hangs off, so that pinned buffers are first-touched there and the PCIe traffic of eight ranks does not cross sockets.
+    Best effort: returns the node, or None when the topology cannot be read."""
+    try:
+        import torch
+        p = torch.cuda.get_device_properties(device_index)
+        bdf = "%04x:%02x:%02x.0" % (p.pci_domain_id, p.pci_bus_id, p.pci_device_id)
+        node = int(open(f"/sys/bus/pci/devices/{bdf}/numa_node").read())
+        if node < 0:
+            return None
+        cpus = set()
+        for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+            lo, _, hi = part.partition("-")
+            cpus.update(range(int(lo), int(hi or lo) + 1))
+        allowed = os.sched_getaffinity(0) & cpus
+        if allowed:
+            os.sched_setaffinity(0, allowed)
+            return node
+    except Exception:
+        pass
+    return None

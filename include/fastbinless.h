@@ -310,6 +310,10 @@ typedef struct {
 } fb_band_out;
 FB_API int FB_NAME(band_export)(fb_handle *h, const fb_band_params *p, fb_band_out *out);
 
+/* Diagnostic: device time (CUDA events on the solver's stream, milliseconds) of the ADMM loop of the last fb_gfl_solve /
+ * fb_gfl_solve_multi call made by this host thread: uploads, set-up and state export are outside it. */
+FB_API double FB_NAME(gfl_last_solve_ms)(void);
+
 /* Device and pinned-host blocks of destroyed handles are kept in a size-keyed cache (cudaMalloc / cudaFree cost
  * milliseconds per call and fast_binless is called once per locus); this returns them to the driver. */
 FB_API void FB_NAME(release_cached_memory)(void);

@@ -1479,6 +1479,7 @@ FB_API int fbo_comm_init(int rank, int world, const void *) {
     g_create_error = "the CPU oracle is a single rank"; return 6;
 }
 FB_API int fbo_comm_destroy(void) { return FB_OK; }
+FB_API double fbo_gfl_last_solve_ms(void) { return 0.0; }
 /* single-process multi-GPU entry points: the reference is one thread on one CPU, so "ngpus" changes nothing here */
 FB_API int fbo_create(int nbins, const fb_mat *mat, fb_handle **out);
 FB_API int fbo_create_multi(int nbins, const fb_mat *mat, int, fb_handle **out) { return fbo_create(nbins, mat, out); }
