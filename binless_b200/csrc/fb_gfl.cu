@@ -886,9 +886,12 @@ GflSolver::~GflSolver() {
         static const char *nm_nccl[7] = {"k_beta", "k_prox", "allreduce", "k_ctl", "pack", "send/recv", "unpack"};
         static const char *nm_p2p[7] = {"k_beta", "k_prox", "allreduce", "k_ctl", "-", "push (peer stores)", "barrier"};
         const char **nm = p2p_ ? nm_p2p : nm_nccl;
-        std::fprintf(stderr, "[fb shard timing] rank %d n=%d, mean over %d sampled iterations (ms):", rank_, g_.n, tcount_);
-        for (int k = 0; k < 7; ++k) std::fprintf(stderr, " %s %.3f", nm[k], tacc_[k] / tcount_);
-        std::fprintf(stderr, "\n");
+        std::string line = "[fb shard timing] rank " + std::to_string(rank_) + " n=" + std::to_string(g_.n) + ", mean over " +
+                           std::to_string(tcount_) + " sampled iterations (ms):";
+        char buf[64];
+        for (int k = 0; k < 7; ++k) { std::snprintf(buf, sizeof buf, " %s %.3f", nm[k], tacc_[k] / tcount_); line += buf; }
+        line += "\n";
+        std::fputs(line.c_str(), stderr);     // one write: the ranks share the terminal
     }
     for (auto &e : tev_) cudaEventDestroy(e);
     if (graph_exec_) cudaGraphExecDestroy(graph_exec_);
