@@ -109,7 +109,10 @@ k_beta(Grid g, const GflCtl *__restrict__ ctl, const double *__restrict__ y, con
 #else
 // Every global load of the tile is issued before the first use (24 per thread in flight): ncu showed the first version
 // stalled on the long scoreboard 61 % of the time with a handful of loads per warp outstanding.
-__global__ void __launch_bounds__(TILE * 8)
+#ifndef FB_BETA_MINB
+#define FB_BETA_MINB 1
+#endif
+__global__ void __launch_bounds__(TILE * 8, FB_BETA_MINB)
 k_beta(Grid g, const GflCtl *__restrict__ ctl, const double *__restrict__ y, const double *__restrict__ w,
        const double *__restrict__ zr, double *__restrict__ ur, const double *__restrict__ zc,
        double *__restrict__ uc, double *__restrict__ beta, double *__restrict__ betaT,

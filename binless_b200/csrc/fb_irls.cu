@@ -22,6 +22,12 @@ __device__ __forceinline__ void bias_decay(const LegTables &L, int i, int j, int
         dc = L.ddiag[j - i];
     }
 }
+// the closed-form tables only (k_leg_pass: the per-cell fallback sums its legs elsewhere, leg_pass_cells)
+__device__ __forceinline__ double log_expected_tab(const LegTables &L, int i, int j, int d, double phi) {
+    const double bi = L.brow[i];
+    const double b = (i == j) ? 2. * bi : bi + L.brow[j];
+    return ((b + L.ddiag[j - i]) + phi) + L.expo[d];
+}
 __device__ __forceinline__ double log_expected(const LegTables &L, int i, int j, int d, int64_t idx, double phi) {
     double b, dc;
     bias_decay(L, i, j, idx, b, dc);
@@ -106,7 +112,7 @@ k_leg_pass(Tri t, LegTables L, double alpha, const int32_t *__restrict__ obs, co
             if (ok[q]) {
                 if (MODE == MODE_NOBS) { a = (double)no[q]; }
                 else {
-                    const double eta = log_expected(L, i, j, d, base + rm_start(i, n) + (j - i), ph[q]);
+                    const double eta = log_expected_tab(L, i, j, d, ph[q]);
                     if (MODE == MODE_RESID) {
                         double z, w;
                         nb_residual(eta, ob[q], no[q], alpha, z, w);
@@ -612,6 +618,18 @@ k_bin_sum(int nb, const int64_t *__restrict__ off, const uint32_t *__restrict__ 
     if (lane == 0) { items[2 * bin] = a; items[2 * bin + 1] = b; }
 }
 
+// exposure leg of the per-cell fallback: the cells of a dataset are one contiguous range; fixed-shape sum
+__global__ void __launch_bounds__(1024)
+k_range_sum(int64_t ncells, const double *__restrict__ ca, const double *__restrict__ cb, double *__restrict__ items) {
+    __shared__ double s[32];
+    const int d = blockIdx.x;
+    double a = 0.0, b = 0.0;
+    for (int64_t i = threadIdx.x; i < ncells; i += blockDim.x) { a += ca[(int64_t)d * ncells + i]; b += cb[(int64_t)d * ncells + i]; }
+    const double ra = block_sum(a, s);
+    const double rb = block_sum(b, s);
+    if (threadIdx.x == 0) { items[2 * d] = ra; items[2 * d + 1] = rb; }
+}
+
 // checkerboard cross-validation: sum and count of chisq = w (phihat - soft(beta, lam1))^2 + lam1^2 over the cells of
 // group g = (bin1 + bin2) % 2 (ScorePreparator.ipp:8-16, Likelihoods.hpp:25-42 with eCprime = 0); one partial per block
 __global__ void __launch_bounds__(EW_THREADS)
@@ -692,7 +710,8 @@ void leg_pass_cells(int mode, const Tri &t, LegTables L, double alpha, const int
     case MODE_POISSON: k_cell_ab<MODE_POISSON><<<ew_grid(t), EW_THREADS, 0, st>>>(t, L, alpha, obs, nobs, phi, ca, cb); break;
     default: k_cell_ab<MODE_NOBS><<<ew_grid(t), EW_THREADS, 0, st>>>(t, L, alpha, obs, nobs, phi, ca, cb); break;
     }
-    k_bin_sum<<<(nb + 3) / 4, 128, 0, st>>>(nb, off, list, ca, cb, items);
+    if (off) k_bin_sum<<<(nb + 3) / 4, 128, 0, st>>>(nb, off, list, ca, cb, items);
+    else k_range_sum<<<nb, 1024, 0, st>>>(t.ncells, ca, cb, items);      // exposure leg: bin = dataset
     FB_LAUNCH_CHECK();
 }
 

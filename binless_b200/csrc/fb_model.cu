@@ -415,10 +415,11 @@ void Model::upload_tables() {
 }
 
 void Model::leg_sums(int leg, int mode, std::vector<double> &a, std::vector<double> &b) {
-    if (generic_ && leg != LEG_EXPO) {
-        const int nb = leg == LEG_BIAS ? nb_bias_ : nb_dec_;
-        leg_pass_cells(mode, t_, tables(tab_), alpha_, obs_.p, nobs_.p, phi_.p, nb, leg == LEG_BIAS ? bias_off_.p : dec_off_.p,
-                       leg == LEG_BIAS ? bias_list_.p : dec_list_.p, cell_a_.p, cell_b_.p, items_.p, st_);
+    if (generic_) {
+        const int nb = leg == LEG_EXPO ? t_.D : (leg == LEG_BIAS ? nb_bias_ : nb_dec_);
+        leg_pass_cells(mode, t_, tables(tab_), alpha_, obs_.p, nobs_.p, phi_.p, nb,
+                       leg == LEG_EXPO ? nullptr : (leg == LEG_BIAS ? bias_off_.p : dec_off_.p),
+                       leg == LEG_EXPO ? nullptr : (leg == LEG_BIAS ? bias_list_.p : dec_list_.p), cell_a_.p, cell_b_.p, items_.p, st_);
         kernel_launches += 2;
         FB_CUDA(cudaMemcpyAsync(items_h_.p, items_.p, 2 * (size_t)nb * sizeof(double), cudaMemcpyDeviceToHost, st_));
         FB_CUDA(cudaStreamSynchronize(st_));

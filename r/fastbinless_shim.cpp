@@ -35,6 +35,19 @@ void check(int rc, const fb_handle *h) {
 void check_interrupt_fn(void *) { R_CheckUserInterrupt(); }
 int interrupt_cb(void *) { return R_ToplevelExec(check_interrupt_fn, nullptr) == FALSE ? 1 : 0; }
 
+// options(binless.ngpus = N): the call shares every fused-lasso solve between N devices of this R process (fb_create_multi);
+// the R signatures of the reference stay as they are
+int option_ngpus() {
+    SEXP v = Rf_GetOption1(Rf_install("binless.ngpus"));
+    if (v == R_NilValue) return 1;
+    const int n = Rf_asInteger(v);
+    return n == NA_INTEGER || n < 1 ? 1 : n;
+}
+int create_handle(unsigned nbins, const fb_mat *m, fb_handle **h) {
+    const int ngpus = option_ngpus();
+    return ngpus > 1 ? fb_create_multi((int)nbins, m, ngpus, h) : fb_create((int)nbins, m, h);
+}
+
 // FastDataCore's view of the data frame (FastData.ipp:5-14): factors arrive as their integer codes
 fb_mat as_fb_mat(const DataFrame &obs, IntegerVector &name, IntegerVector &bin1, IntegerVector &pos1,
                  IntegerVector &bin2, IntegerVector &pos2, IntegerVector &observed, IntegerVector &nobs,
@@ -71,8 +84,8 @@ List fast_binless_cuda(const DataFrame obs, unsigned nbins, double alpha, const 
     NumericVector distance;
     fb_mat m = as_fb_mat(obs, name, bin1, pos1, bin2, pos2, observed, nobs, distance);
     HandleGuard g;
-    check(fb_create((int)nbins, &m, &g.h), nullptr);
-    fb_set_interrupt_cb(g.h, interrupt_cb, nullptr);
+    check(create_handle(nbins, &m, &g.h), nullptr);
+    fb_set_interrupt_cb(g.h, interrupt_cb, nullptr);   // refused (and not needed) on a multi-GPU handle
     const R_xlen_t N = m.N;
     const int D = Rcpp::max(name);
     // csv_out: the reference streams the seven computed columns to the (gzip) file and returns mat = 1
@@ -122,7 +135,7 @@ DataFrame fast_binless_difference_cuda(const List out, int ref, double alpha, co
     NumericVector distance;
     fb_mat m = as_fb_mat(obs, name, bin1, pos1, bin2, pos2, observed, nobs, distance);
     HandleGuard g;
-    check(fb_create((int)nbins, &m, &g.h), nullptr);
+    check(create_handle(nbins, &m, &g.h), nullptr);
     // set_state calls of fast_binless.cpp:244-260
     NumericVector log_signal = out["log_signal"];
     List lb = out["biases"], ld = out["decay"], le = out["exposures"];

@@ -5,7 +5,7 @@ echo rc=$?
 grep -E "fb shard" gpurun_out/r2_bench_${N}gpu.err | sort | uniq -c | sort -rn | head -12
 python - <<PY
 import json
-d=json.load(open('gpurun_out/r2_bench_${N}gpu.json'))
+d=json.loads([l for l in open('gpurun_out/r2_bench_${N}gpu.json') if l.startswith('{')][-1])
 for k in ('n_gpus','value','ms_per_step','e2e','c3_sweep','c4_trailblock','single_process_2gpu_bit_identical'):
     print(k, d.get(k))
 c=d.get('c5_chromosome'); 

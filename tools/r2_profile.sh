@@ -12,3 +12,7 @@ for it in 2 9 17; do
       -o gpurun_out/${tag}_admm_it$it -f python tools/profile_target.py > gpurun_out/${tag}_ncu_it$it.log 2>&1
 done
 ls -la gpurun_out | grep $tag
+# IRLS leg passes (residual mode) of the second outer step
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:k_leg_pass --launch-skip 9 --launch-count 3 \
+    -o gpurun_out/${tag}_irls -f python tools/profile_target.py > gpurun_out/${tag}_ncu_irls.log 2>&1
+ls -la gpurun_out | grep ${tag}_irls
