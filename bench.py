@@ -47,13 +47,17 @@ ADMM_BYTES_PER_CELL_ITER = 104  # DESIGN.md section 4 / SURVEY.md section 8(d)
 
 
 def ncu_traffic():
-    """DRAM bytes (read + write) of one ADMM iteration from the committed `ncu --set full` capture (profiles/)."""
-    path = os.path.join(ROOT, "profiles", "r1s_admm_iteration_ncu_full_summary.json")
-    try:
-        rows = json.load(open(path))
-        return int(sum((r["dram_read_MB"] + r["dram_write_MB"]) * 1e6 for r in rows))
-    except Exception:
-        return None
+    """DRAM bytes (read + write) of one ADMM iteration from the committed `ncu --set full` captures (profiles/): the mean over
+    an early, a middle and a late iteration of the first solve (k_beta + the chain-prox kernel that ran + k_ctl)."""
+    tot = []
+    for it in (2, 9, 17):
+        path = os.path.join(ROOT, "profiles", f"r2_admm_it{it}_ncu_full_summary.json")
+        try:
+            rows = json.load(open(path))
+            tot.append(sum((r["dram_read_MB"] + r["dram_write_MB"]) * 1e6 for r in rows))
+        except Exception:
+            pass
+    return int(sum(tot) / len(tot)) if tot else None
 
 
 def measured_peak():
@@ -248,9 +252,9 @@ def run_cuda(args):
         "clocks": clk,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": ncu_traffic(), "peak_source": peak_src,
-                     "traffic_source": "ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum of k_beta + k_prox + k_ctl, "
-                                       "one iteration (profiles/r1s_admm_iteration_ncu_full_summary.json)",
-                     "kernel": "ADMM iteration of the fused-lasso solve (GflSolver::iteration = k_beta + k_prox + k_ctl)",
+                     "traffic_source": "ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum of k_beta + chain prox + k_ctl, mean of "
+                                       "iterations 2 / 9 / 17 of the first solve (profiles/r2_admm_it*_ncu_full_summary.json)",
+                     "kernel": "ADMM iteration of the fused-lasso solve (GflSolver::iteration = k_beta + k_prox | k_prox_aset + k_ctl)",
                      "bytes_per_launch": ADMM_BYTES_PER_CELL_ITER * ncells, "us_per_launch": sec_per_iter * 1e6,
                      "solver_share_of_device_time": ms_solver / max(ms_dev, 1e-9)},
     }
