@@ -72,11 +72,12 @@ __device__ __forceinline__ double block_sum(double v, double *s /*[32]*/) {
 template <int LEG, int MODE>
 __global__ void __launch_bounds__(TILE_J)
 k_leg_pass(Tri t, LegTables L, double alpha, const int32_t *__restrict__ obs, const int32_t *__restrict__ nobs,
-           const double *__restrict__ phi, double *__restrict__ part) {
+           const double *__restrict__ phi, double *__restrict__ part, const int grp_rank, const int grp_world) {
     const int tJ = blockIdx.x, tI = blockIdx.y, d = blockIdx.z;
     const int ntJ = gridDim.x, ntI = gridDim.y;
     const int i0 = tI * TILE_I, j0 = tJ * TILE_J;
     if (j0 + TILE_J - 1 < i0) return; // tile entirely below the diagonal
+    if (((tI % LEG_GROUPS) % grp_world) != grp_rank) return;   // a tile row of a group another GPU sums (IRLS legs sharded)
     const int tx = threadIdx.x, lane = tx & 31, wid = tx >> 5;
     const int j = j0 + tx;
     const int n = t.n;
@@ -167,56 +168,68 @@ k_leg_pass(Tri t, LegTables L, double alpha, const int32_t *__restrict__ obs, co
     }
 }
 
-// finalize: fixed-order sums of the tile partials into per-item pairs
+// finalize: fixed-order sums of the tile partials into per-item pairs. The sums have a two-level shape that does not
+// depend on how many GPUs share the call: tile row tI belongs to group tI mod LEG_GROUPS; level 1 adds the partials of one
+// group (one warp or block per (item, group): lane / thread strided, then a butterfly), level 2 adds the LEG_GROUPS group
+// sums in order. One GPU computes every group itself; `world` GPUs (world divides LEG_GROUPS) compute the groups
+// g mod world == rank each, all-gather the group sums and form the same level-2 sum: bit-identical results.
+__device__ __forceinline__ bool group_is_mine(int g, int grp_rank, int grp_world) { return (g % grp_world) == grp_rank; }
+
 __global__ void __launch_bounds__(256)
-k_fin_expo(Tri t, int ntI, int ntJ, const double *__restrict__ part, double *__restrict__ items) {
+k_fin_expo(Tri t, int ntI, int ntJ, const double *__restrict__ part, double *__restrict__ items_g, int grp_rank, int grp_world) {
     __shared__ double s_red[2][32];
-    const int d = blockIdx.x;
+    const int d = blockIdx.x, g = blockIdx.y;
+    if (!group_is_mine(g, grp_rank, grp_world)) return;
+    const int nti_g = ntI > g ? (ntI - g + LEG_GROUPS - 1) / LEG_GROUPS : 0;
     double a = 0.0, b = 0.0;
-    for (int k = threadIdx.x; k < ntI * ntJ; k += blockDim.x) {
-        const int tI = k / ntJ, tJ = k % ntJ;
+    for (int k = threadIdx.x; k < nti_g * ntJ; k += blockDim.x) {
+        const int tI = g + LEG_GROUPS * (k / ntJ), tJ = k % ntJ;
         if (tJ * TILE_J + TILE_J - 1 < tI * TILE_I) continue;
         const int64_t p = ((int64_t)(d * ntI + tI) * ntJ + tJ) * 2;
         a += part[p]; b += part[p + 1];
     }
     a = block_sum(a, s_red[0]); b = block_sum(b, s_red[1]);
-    if (threadIdx.x == 0) { items[2 * d] = a; items[2 * d + 1] = b; }
+    if (threadIdx.x == 0) { items_g[((int64_t)g * t.D + d) * 2] = a; items_g[((int64_t)g * t.D + d) * 2 + 1] = b; }
 }
 
-// one warp per bin: the row partials (by tile column) and column partials (by tile row) of every dataset, lane-strided
-// and then a butterfly sum: a fixed shape, so the result is the same on every run
+// one warp per (bin, group): the row partials (by tile column; they all come from the tile row of the bin) and the
+// column partials (by tile row) of every dataset
 __global__ void __launch_bounds__(128)
-k_fin_bias(Tri t, int ntI, int ntJ, const double *__restrict__ part, double *__restrict__ items) {
+k_fin_bias(Tri t, int ntI, int ntJ, const double *__restrict__ part, double *__restrict__ items_g, int grp_rank, int grp_world) {
     const int r = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int g = blockIdx.y;
     const int lane = threadIdx.x & 31;
     const int n = t.n;
-    if (r >= n) return;
+    if (r >= n || !group_is_mine(g, grp_rank, grp_world)) return;
     const double2 *rp = reinterpret_cast<const double2 *>(part);
     const double2 *cp = reinterpret_cast<const double2 *>(part + (int64_t)t.D * ntJ * n * 2);
     const int tj_min = ((r / TILE_I) * TILE_I) / TILE_J;
     int ti_max = ((r / TILE_J) * TILE_J + TILE_J - 1) / TILE_I;
     if (ti_max > ntI - 1) ti_max = ntI - 1;
-    const int nrow = ntJ - tj_min, ncol = ti_max + 1, per = nrow + ncol;
+    const int nrow = (((r / TILE_I) % LEG_GROUPS) == g) ? ntJ - tj_min : 0;
+    const int ncol = ti_max >= g ? (ti_max - g) / LEG_GROUPS + 1 : 0, per = nrow + ncol;
     double a = 0.0, b = 0.0;
     for (int q = lane; q < t.D * per; q += 32) {
         const int d = q / per, k = q - d * per;
         const double2 v = k < nrow ? __ldg(rp + ((int64_t)(d * ntJ + tj_min + k) * n + r))
-                                   : __ldg(cp + ((int64_t)(d * ntI + (k - nrow)) * n + r));
+                                   : __ldg(cp + ((int64_t)(d * ntI + g + LEG_GROUPS * (k - nrow)) * n + r));
         a += v.x; b += v.y;
     }
     a = warp_sum(a); b = warp_sum(b);
-    if (lane == 0) { items[2 * r] = a; items[2 * r + 1] = b; }
+    if (lane == 0) { items_g[((int64_t)g * n + r) * 2] = a; items_g[((int64_t)g * n + r) * 2 + 1] = b; }
 }
 
-// one warp per diagonal
+// one warp per (diagonal, group)
 __global__ void __launch_bounds__(128)
-k_fin_decay(Tri t, int ntI, int ntJ, const double *__restrict__ part, double *__restrict__ items) {
+k_fin_decay(Tri t, int ntI, int ntJ, const double *__restrict__ part, double *__restrict__ items_g, int grp_rank, int grp_world) {
     const int k = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int g = blockIdx.y;
     const int lane = threadIdx.x & 31;
-    if (k >= t.n) return;
+    if (k >= t.n || !group_is_mine(g, grp_rank, grp_world)) return;
+    const int nti_g = ntI > g ? (ntI - g + LEG_GROUPS - 1) / LEG_GROUPS : 0;
     double a = 0.0, b = 0.0;
-    for (int q = lane; q < t.D * ntI; q += 32) {
-        const int d = q / ntI, tI = q % ntI;
+    for (int q = lane; q < t.D * nti_g; q += 32) {
+        const int d = q / nti_g, tI = g + LEG_GROUPS * (q % nti_g);
         const int i0 = tI * TILE_I;
         const int hi = k + i0 + (TILE_I - 1);          // j0 <= hi
         const int lo = hi - (TILE_DIAGS - 2);          // j0 >= lo  (slot <= 158)
@@ -232,7 +245,18 @@ k_fin_decay(Tri t, int ntI, int ntJ, const double *__restrict__ part, double *__
         }
     }
     a = warp_sum(a); b = warp_sum(b);
-    if (lane == 0) { items[2 * k] = a; items[2 * k + 1] = b; }
+    if (lane == 0) { items_g[((int64_t)g * t.n + k) * 2] = a; items_g[((int64_t)g * t.n + k) * 2 + 1] = b; }
+}
+
+// level 2: the group sums in order
+__global__ void __launch_bounds__(256)
+k_sum_groups(int nitems, const double *__restrict__ items_g, double *__restrict__ items) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= 2 * nitems) return;
+    double v = 0.0;
+#pragma unroll
+    for (int g = 0; g < LEG_GROUPS; ++g) v += items_g[(int64_t)g * 2 * nitems + i];
+    items[i] = v;
 }
 
 // --------------------------------------------------------------------------
@@ -669,12 +693,12 @@ inline dim3 tile_grid(const Tri &t) { return dim3((unsigned)tiles_j(t.n), (unsig
 
 template <int LEG>
 void leg_pass_mode(int mode, const Tri &t, LegTables L, double alpha, const int32_t *obs, const int32_t *nobs,
-                   const double *phi, double *part, cudaStream_t st) {
+                   const double *phi, double *part, int grp_rank, int grp_world, cudaStream_t st) {
     const dim3 g = tile_grid(t);
     switch (mode) {
-    case MODE_RESID: k_leg_pass<LEG, MODE_RESID><<<g, TILE_J, 0, st>>>(t, L, alpha, obs, nobs, phi, part); break;
-    case MODE_POISSON: k_leg_pass<LEG, MODE_POISSON><<<g, TILE_J, 0, st>>>(t, L, alpha, obs, nobs, phi, part); break;
-    default: k_leg_pass<LEG, MODE_NOBS><<<g, TILE_J, 0, st>>>(t, L, alpha, obs, nobs, phi, part); break;
+    case MODE_RESID: k_leg_pass<LEG, MODE_RESID><<<g, TILE_J, 0, st>>>(t, L, alpha, obs, nobs, phi, part, grp_rank, grp_world); break;
+    case MODE_POISSON: k_leg_pass<LEG, MODE_POISSON><<<g, TILE_J, 0, st>>>(t, L, alpha, obs, nobs, phi, part, grp_rank, grp_world); break;
+    default: k_leg_pass<LEG, MODE_NOBS><<<g, TILE_J, 0, st>>>(t, L, alpha, obs, nobs, phi, part, grp_rank, grp_world); break;
     }
 }
 
@@ -686,22 +710,32 @@ size_t leg_part_doubles(const Tri &t) {
     return std::max(e, std::max(b, dc));
 }
 
-void leg_pass(int leg, int mode, const Tri &t, LegTables L, double alpha, const int32_t *obs, const int32_t *nobs,
-              const double *phi, double *part, double *items, cudaStream_t st) {
+void leg_pass_groups(int leg, int mode, const Tri &t, LegTables L, double alpha, const int32_t *obs, const int32_t *nobs,
+                     const double *phi, double *part, double *items_g, int grp_rank, int grp_world, cudaStream_t st) {
     const int ntI = tiles_i(t.n), ntJ = tiles_j(t.n);
     if (leg == LEG_EXPO) {
-        leg_pass_mode<LEG_EXPO>(mode, t, L, alpha, obs, nobs, phi, part, st);
-        k_fin_expo<<<t.D, 256, 0, st>>>(t, ntI, ntJ, part, items);
+        leg_pass_mode<LEG_EXPO>(mode, t, L, alpha, obs, nobs, phi, part, grp_rank, grp_world, st);
+        k_fin_expo<<<dim3(t.D, LEG_GROUPS), 256, 0, st>>>(t, ntI, ntJ, part, items_g, grp_rank, grp_world);
     } else if (leg == LEG_BIAS) {
-        leg_pass_mode<LEG_BIAS>(mode, t, L, alpha, obs, nobs, phi, part, st);
-        k_fin_bias<<<(t.n + 3) / 4, 128, 0, st>>>(t, ntI, ntJ, part, items);
+        leg_pass_mode<LEG_BIAS>(mode, t, L, alpha, obs, nobs, phi, part, grp_rank, grp_world, st);
+        k_fin_bias<<<dim3((t.n + 3) / 4, LEG_GROUPS), 128, 0, st>>>(t, ntI, ntJ, part, items_g, grp_rank, grp_world);
     } else {
-        leg_pass_mode<LEG_DECAY>(mode, t, L, alpha, obs, nobs, phi, part, st);
-        k_fin_decay<<<(t.n + 3) / 4, 128, 0, st>>>(t, ntI, ntJ, part, items);
+        leg_pass_mode<LEG_DECAY>(mode, t, L, alpha, obs, nobs, phi, part, grp_rank, grp_world, st);
+        k_fin_decay<<<dim3((t.n + 3) / 4, LEG_GROUPS), 128, 0, st>>>(t, ntI, ntJ, part, items_g, grp_rank, grp_world);
     }
     FB_LAUNCH_CHECK();
 }
 
+void leg_pass_combine(int nitems, const double *items_g, double *items, cudaStream_t st) {
+    k_sum_groups<<<(2 * nitems + 255) / 256, 256, 0, st>>>(nitems, items_g, items);
+    FB_LAUNCH_CHECK();
+}
+
+void leg_pass(int leg, int mode, const Tri &t, LegTables L, double alpha, const int32_t *obs, const int32_t *nobs,
+              const double *phi, double *part, double *items_g, double *items, cudaStream_t st) {
+    leg_pass_groups(leg, mode, t, L, alpha, obs, nobs, phi, part, items_g, 0, 1, st);
+    leg_pass_combine(leg == LEG_EXPO ? t.D : t.n, items_g, items, st);
+}
 
 void leg_pass_cells(int mode, const Tri &t, LegTables L, double alpha, const int32_t *obs, const int32_t *nobs, const double *phi,
                     int nb, const int64_t *off, const uint32_t *list, double *ca, double *cb, double *items, cudaStream_t st) {

@@ -57,8 +57,16 @@ size_t leg_part_doubles(const Tri &t);
 //   MODE_NOBS    a = nobs,       b = 0
 // Result: items[2*item], items[2*item+1] for item in [0, D) / [0, n) / [0, n).
 // Fixed-shape reduction: same bits on every run.
+// The sums have a two-level shape independent of the number of GPUs: tile row tI is in group tI mod LEG_GROUPS; items_g
+// (LEG_GROUPS x 2 x nitems doubles) receives the sums of the groups g with g mod grp_world == grp_rank (leg_pass_groups);
+// after the other groups have been gathered from their owners, leg_pass_combine adds the groups in order. leg_pass does
+// both on one GPU. nitems = D for the exposure leg, n otherwise.
+constexpr int LEG_GROUPS = 8;
+void leg_pass_groups(int leg, int mode, const Tri &t, LegTables L, double alpha, const int32_t *obs, const int32_t *nobs,
+                     const double *phi, double *part, double *items_g, int grp_rank, int grp_world, cudaStream_t st);
+void leg_pass_combine(int nitems, const double *items_g, double *items, cudaStream_t st);
 void leg_pass(int leg, int mode, const Tri &t, LegTables L, double alpha, const int32_t *obs, const int32_t *nobs,
-              const double *phi, double *part, double *items, cudaStream_t st);
+              const double *phi, double *part, double *items_g, double *items, cudaStream_t st);
 
 // The same sums in the per-cell fallback, for the bias / decay leg: `off` / `list` are the CSR cell lists of the nb leg bins
 // (bit 31 of an entry: the cell counts twice), ca / cb two N-double scratch arrays; items[2*bin], items[2*bin+1].

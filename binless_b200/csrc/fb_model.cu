@@ -167,6 +167,7 @@ void Model::alloc_tables() {
     tab_.alloc(tn); tab_old_.alloc(tn); tab_h_.alloc(tn);
     const size_t items = 2 * (size_t)std::max<int64_t>(std::max<int64_t>(n, D), std::max(tab_b_, tab_d_));
     items_.alloc(items); items_h_.alloc(items);
+    items_g_.alloc((size_t)LEG_GROUPS * items);
 }
 
 Model::~Model() { close_stream(); }
@@ -427,8 +428,21 @@ void Model::leg_sums(int leg, int mode, std::vector<double> &a, std::vector<doub
         for (int k = 0; k < nb; ++k) { a[k] = items_h_.p[2 * k]; b[k] = items_h_.p[2 * k + 1]; }
         return;
     }
-    leg_pass(leg, mode, t_, tables(tab_), alpha_, obs_.p, nobs_.p, phi_.p, part_.p, items_.p, st_);
-    kernel_launches += 2;
+    // IRLS legs shared between the GPUs of the communicator: every rank sums the tile rows of its groups, the group sums
+    // are gathered (one small broadcast per group from its owner), and everybody adds the groups in the same order: the
+    // result has the bits of the single-GPU sum (fb_irls.cuh). Needs a world size that divides LEG_GROUPS.
+    Comm &cm = Comm::get();
+    const bool shared = cm.active() && LEG_GROUPS % cm.world() == 0 && !std::getenv("FB_IRLS_REPLICATED");
+    const int nit = leg == LEG_EXPO ? t_.D : t_.n;
+    leg_pass_groups(leg, mode, t_, tables(tab_), alpha_, obs_.p, nobs_.p, phi_.p, part_.p, items_g_.p, shared ? cm.rank() : 0,
+                    shared ? cm.world() : 1, st_);
+    if (shared) {
+        cm.group_start();
+        for (int g = 0; g < LEG_GROUPS; ++g) cm.bcast(items_g_.p + (size_t)g * 2 * nit, 2 * (size_t)nit, g % cm.world(), st_);
+        cm.group_end();
+    }
+    leg_pass_combine(nit, items_g_.p, items_.p, st_);
+    kernel_launches += 1;
     const int nitems = leg == LEG_EXPO ? t_.D : t_.n;
     FB_CUDA(cudaMemcpyAsync(items_h_.p, items_.p, 2 * (size_t)nitems * sizeof(double), cudaMemcpyDeviceToHost, st_));
     FB_CUDA(cudaStreamSynchronize(st_));

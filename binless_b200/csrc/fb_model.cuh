@@ -75,7 +75,7 @@ private:
     // device leg tables: [brow n | ddiag n | expo D], current and the copy taken before the decay update
     DevBuf<double> tab_, tab_old_;
     PinBuf<double> tab_h_, items_h_, prec_h_;
-    DevBuf<double> part_, items_, scratch_;
+    DevBuf<double> part_, items_, items_g_, scratch_;   // items_g_: the per-group sums of a leg pass (fb_irls.cuh)
     DevBuf<long long> keys_;
 
     // per-cell fallback (util.cpp:56-111 bins every cell): set by ingest when pos / distance are not
