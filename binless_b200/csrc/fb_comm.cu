@@ -10,7 +10,7 @@ namespace fb {
 namespace {
 // the subset of nccl.h this library calls (NCCL 2.x ABI: enums are ints, ncclUniqueId is 128 opaque bytes)
 struct UniqueId { char internal[128]; };
-enum { kNcclSum = 0, kNcclFloat64 = 8 };
+enum { kNcclSum = 0, kNcclMax = 2, kNcclMin = 3, kNcclInt64 = 4, kNcclFloat64 = 8 };
 using fn_get_uid = int (*)(UniqueId *);
 using fn_init_rank = int (*)(void **, int, UniqueId, int);
 using fn_destroy = int (*)(void *);
@@ -119,6 +119,10 @@ void Comm::recv(double *p, size_t n, int peer, cudaStream_t s) {
 void Comm::allreduce_sum(const double *src, double *dst, size_t n, cudaStream_t s) {
     need();
     FB_NCCL(reinterpret_cast<fn_allreduce>(fn_[F_ALLREDUCE])(src, dst, n, kNcclFloat64, kNcclSum, comm_, s));
+}
+void Comm::allreduce_i64(long long *buf, size_t n, bool take_max, cudaStream_t s) {
+    need();
+    FB_NCCL(reinterpret_cast<fn_allreduce>(fn_[F_ALLREDUCE])(buf, buf, n, kNcclInt64, take_max ? kNcclMax : kNcclMin, comm_, s));
 }
 void Comm::bcast(double *p, size_t n, int root, cudaStream_t s) {
     need();

@@ -40,6 +40,7 @@ public:
     void recv(double *p, size_t n, int peer, cudaStream_t s);
     void allreduce_sum(const double *src, double *dst, size_t n, cudaStream_t s);
     void bcast(double *p, size_t n, int root, cudaStream_t s);
+    void allreduce_i64(long long *buf, size_t n, bool take_max, cudaStream_t s);   // in place; exact in any order
     // CUDA IPC mapping of a peer's allocation, kept for the life of the communicator (opening one costs tens of
     // milliseconds; the solver of every solve asks for the same blocks again); nullptr when it cannot be opened
     void *ipc_open(const cudaIpcMemHandle_t &h);

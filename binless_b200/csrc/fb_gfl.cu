@@ -566,8 +566,12 @@ __global__ void k_band_gather(Grid g, int nbins, const double *__restrict__ tri,
 }
 // sum of w*y and w over the cells outside the band, per row partials
 __global__ void k_band_outside_sums(Grid g, int nbins, const double *__restrict__ y, const double *__restrict__ w,
-                                    double *__restrict__ partial) {
+                                    double *__restrict__ partial, const int sh_rank, const int sh_world) {
     const int i = blockIdx.x;
+    if ((i % sh_world) != sh_rank) {     // a row of another GPU of the communicator: an exact zero in the all-reduce
+        if (threadIdx.x == 0) { partial[2 * i] = 0.0; partial[2 * i + 1] = 0.0; }
+        return;
+    }
     __shared__ double s_a[256], s_b[256];
     double a = 0.0, b = 0.0;
     const int64_t src = rm_start(i, nbins);
@@ -1029,7 +1033,9 @@ int GflSolver::optimize(const double *d_y_tri, const double *d_w_tri, double lam
     cold_ = false;
     if (sharded_) allgather_rows(beta_.p);   // every rank continues with the whole solution
     if (trapeze_) { // average of the far region (fill_triangle)
-        k_band_outside_sums<<<nbins_, 256, 0, st_>>>(g_, nbins_, d_y_tri, d_w_tri, band_partials_.p);
+        // the rows of the far region are dealt to the ranks; the per-row sums of the others arrive as x + 0 (exact)
+        k_band_outside_sums<<<nbins_, 256, 0, st_>>>(g_, nbins_, d_y_tri, d_w_tri, band_partials_.p, sharded_ ? rank_ : 0, sharded_ ? world_ : 1);
+        if (sharded_) Comm::get().allreduce_sum(band_partials_.p, band_partials_.p, 2 * (size_t)nbins_, st_);
         k_band_avg<<<1, 32, 0, st_>>>(nbins_, band_partials_.p, fillavg_.p);
         kernel_launches += 2;
     }

@@ -286,13 +286,14 @@ k_signal_yw(Tri t, LegTables L, double alpha, const int32_t *__restrict__ obs, c
 
 __global__ void __launch_bounds__(EW_THREADS)
 k_precision(Tri t, LegTables Lo, LegTables Ln, const double *__restrict__ phi_old, const double *__restrict__ phi_new,
-            long long *__restrict__ keys) {
+            long long *__restrict__ keys, const int sh_rank, const int sh_world) {
     const double INF = __longlong_as_double(0x7ff0000000000000LL);
     double dabs = -INF, mx = -INF, mn = INF;
     // a block walks rows blockIdx.y, blockIdx.y + gridDim.y, ... (a mix of long and short rows) and reduces once:
     // one block per row spent most of its time in the reduction (28 800 blocks at 2400 bins x 4)
     const int d = blockIdx.z, n = t.n;
     for (int i = blockIdx.y; i < n; i += gridDim.y) {
+        if ((i % sh_world) != sh_rank) continue;      // rows of another GPU of the communicator
         const int64_t rowbase = (int64_t)d * t.ncells + rm_start(i, n);
         for (int off = threadIdx.x; off < n - i; off += EW_THREADS) {
             const int j = i + off;
@@ -329,10 +330,12 @@ __global__ void k_precision_fin(const long long *keys, double *out3) {
 
 // minima per (dataset, row-or-column index) and (dataset, diagonal): tile kernel like the leg pass
 __global__ void __launch_bounds__(TILE_J)
-k_minima(Tri t, const double *__restrict__ phi, long long *__restrict__ rowkey, long long *__restrict__ diagkey) {
+k_minima(Tri t, const double *__restrict__ phi, long long *__restrict__ rowkey, long long *__restrict__ diagkey,
+         const int sh_rank, const int sh_world) {
     const int tJ = blockIdx.x, tI = blockIdx.y, d = blockIdx.z;
     const int i0 = tI * TILE_I, j0 = tJ * TILE_J;
     if (j0 + TILE_J - 1 < i0) return;
+    if ((tI % sh_world) != sh_rank) return;
     const int tx = threadIdx.x, lane = tx & 31, wid = tx >> 5, n = t.n;
     const int j = j0 + tx;
     const double INF = __longlong_as_double(0x7ff0000000000000LL);
@@ -385,8 +388,9 @@ k_degen_apply(Tri t, double *__restrict__ phi, const long long *__restrict__ row
     }
 }
 __global__ void __launch_bounds__(EW_THREADS)
-k_dataset_min(Tri t, const double *__restrict__ phi, long long *__restrict__ key) {
+k_dataset_min(Tri t, const double *__restrict__ phi, long long *__restrict__ key, const int sh_rank, const int sh_world) {
     const double INF = __longlong_as_double(0x7ff0000000000000LL);
+    if (((int)blockIdx.y % sh_world) != sh_rank) return;
     double mn = INF;
     EW_FOREACH_CELL(t) { (void)j; mn = fmin(mn, phi[rowbase + off]); }
     mn = warp_min(mn);
@@ -410,8 +414,13 @@ k_shift_apply(Tri t, double *__restrict__ phi, const long long *__restrict__ key
 // centring: fixed grid of partial dot products, then one block
 constexpr int CENTER_BLOCKS = 1024;
 __global__ void __launch_bounds__(256)
-k_center_partial(int64_t ncells, const int32_t *__restrict__ nobs, const double *__restrict__ beta, double *__restrict__ scratch) {
+k_center_partial(int64_t ncells, const int32_t *__restrict__ nobs, const double *__restrict__ beta, double *__restrict__ scratch,
+                 const int sh_rank, const int sh_world) {
     __shared__ double s_red[2][32];
+    if (((int)blockIdx.x % sh_world) != sh_rank) {      // a block of another GPU: an exact zero in the all-reduce
+        if (threadIdx.x == 0) { scratch[2 * blockIdx.x] = 0.0; scratch[2 * blockIdx.x + 1] = 0.0; }
+        return;
+    }
     double a = 0.0, b = 0.0;
     for (int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; c < ncells; c += (int64_t)gridDim.x * blockDim.x) {
         const double no = (double)nobs[c];
@@ -762,35 +771,40 @@ void signal_yw(const Tri &t, LegTables L, double alpha, const int32_t *obs, cons
     FB_LAUNCH_CHECK();
 }
 
-void center_dataset(int64_t ncells, const int32_t *nobs_d, double *beta_d, double *scratch, cudaStream_t st) {
-    k_center_partial<<<CENTER_BLOCKS, 256, 0, st>>>(ncells, nobs_d, beta_d, scratch);
+void center_dataset(int64_t ncells, const int32_t *nobs_d, double *beta_d, double *scratch, cudaStream_t st, const Share &sh) {
+    k_center_partial<<<CENTER_BLOCKS, 256, 0, st>>>(ncells, nobs_d, beta_d, scratch, sh.rank, sh.world);
+    if (sh.on()) sh.cm->allreduce_sum(scratch, scratch, 2 * CENTER_BLOCKS, st);
     k_center_final<<<1, CENTER_BLOCKS, 0, st>>>(scratch);
     k_center_apply<<<CENTER_BLOCKS, 256, 0, st>>>(ncells, beta_d, scratch);
     FB_LAUNCH_CHECK();
 }
 
 void precision(const Tri &t, LegTables Lold, LegTables Lnew, const double *phi_old, const double *phi_new,
-               double *scratch, double *out3, cudaStream_t st) {
+               double *scratch, double *out3, cudaStream_t st, const Share &sh) {
     long long *keys = reinterpret_cast<long long *>(scratch);
     k_precision_init<<<1, 1, 0, st>>>(keys);
-    k_precision<<<dim3(1, (unsigned)std::min(t.n, 592), (unsigned)t.D), EW_THREADS, 0, st>>>(t, Lold, Lnew, phi_old, phi_new, keys);
+    k_precision<<<dim3(1, (unsigned)std::min(t.n, 592), (unsigned)t.D), EW_THREADS, 0, st>>>(t, Lold, Lnew, phi_old, phi_new, keys,
+                                                                                         sh.rank, sh.world);
+    if (sh.on()) { sh.cm->allreduce_i64(keys, 2, true, st); sh.cm->allreduce_i64(keys + 2, 1, false, st); }
     k_precision_fin<<<1, 1, 0, st>>>(keys, out3);
     FB_LAUNCH_CHECK();
 }
 
-void remove_degeneracy(const Tri &t, double *phi, long long *keys, cudaStream_t st) {
+void remove_degeneracy(const Tri &t, double *phi, long long *keys, cudaStream_t st, const Share &sh) {
     const double INF = INFINITY;
     const int64_t nk = (int64_t)2 * t.n * t.D;
     k_fill_keys<<<(unsigned)((nk + 255) / 256), 256, 0, st>>>(keys, nk, INF);
     long long *rowkey = keys, *diagkey = keys + (int64_t)t.n * t.D;
-    k_minima<<<tile_grid(t), TILE_J, 0, st>>>(t, phi, rowkey, diagkey);
+    k_minima<<<tile_grid(t), TILE_J, 0, st>>>(t, phi, rowkey, diagkey, sh.rank, sh.world);
+    if (sh.on()) sh.cm->allreduce_i64(keys, (size_t)nk, false, st);
     k_degen_apply<<<ew_grid(t), EW_THREADS, 0, st>>>(t, phi, rowkey, diagkey);
     FB_LAUNCH_CHECK();
 }
 
-void shift_signal(const Tri &t, double *phi, long long *keys, cudaStream_t st) {
+void shift_signal(const Tri &t, double *phi, long long *keys, cudaStream_t st, const Share &sh) {
     k_fill_keys<<<(t.D + 255) / 256, 256, 0, st>>>(keys, t.D, INFINITY);
-    k_dataset_min<<<ew_grid(t), EW_THREADS, 0, st>>>(t, phi, keys);
+    k_dataset_min<<<ew_grid(t), EW_THREADS, 0, st>>>(t, phi, keys, sh.rank, sh.world);
+    if (sh.on()) sh.cm->allreduce_i64(keys, (size_t)t.D, false, st);
     k_shift_apply<<<ew_grid(t), EW_THREADS, 0, st>>>(t, phi, keys);
     FB_LAUNCH_CHECK();
 }

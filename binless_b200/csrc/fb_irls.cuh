@@ -22,6 +22,7 @@
 // row/column r falls in), ddiag[n] (decay of diagonal k), expo[D].
 #pragma once
 #include "fb_util.cuh"
+#include "fb_comm.cuh"
 
 namespace fb {
 
@@ -38,6 +39,15 @@ struct LegTables {
     // per-cell fallback: when cb1 is set, brow is indexed by BIAS BIN and ddiag by DECAY BIN, and every
     // cell carries the int32 bins of pos1 / pos2 / log(distance) (util.cpp:56-111 semantics); else null
     const int32_t *cb1 = nullptr, *cb2 = nullptr, *cdb = nullptr;
+};
+
+// The GPUs of a communicator share the REDUCTION passes of the outer loop (every rank holds the whole matrix): rank r reads
+// the rows / tile rows / blocks r, r + world, ...; the per-rank results are combined exactly (integer min / max keys; sums
+// whose other addends are exact zeros), so the outcome has the bits of the single-GPU pass. Default: one GPU.
+struct Share {
+    int rank = 0, world = 1;
+    Comm *cm = nullptr;
+    bool on() const { return cm != nullptr && world > 1; }
 };
 
 enum { LEG_EXPO = 0, LEG_BIAS = 1, LEG_DECAY = 2 };
@@ -84,15 +94,15 @@ void signal_yw(const Tri &t, LegTables L, double alpha, const int32_t *obs, cons
                unsigned group, double *y, double *w, cudaStream_t st);
 
 // beta[d] -= sum(beta*nobs)/sum(nobs) (fast_binless.ipp:33-44); scratch >= 2*1024+2 doubles
-void center_dataset(int64_t ncells, const int32_t *nobs_d, double *beta_d, double *scratch, cudaStream_t st);
+void center_dataset(int64_t ncells, const int32_t *nobs_d, double *beta_d, double *scratch, cudaStream_t st, const Share &sh = Share());
 
 // abs = max|eta_new - eta_old|, max eta_new, min eta_new; out3 = device {abs, max, min}
 void precision(const Tri &t, LegTables Lold, LegTables Lnew, const double *phi_old, const double *phi_new,
-               double *scratch, double *out3, cudaStream_t st);
+               double *scratch, double *out3, cudaStream_t st, const Share &sh = Share());
 
 // remove_signal_degeneracy / shift_signal, in place on phi; keys: (2n+1)*D int64 scratch
-void remove_degeneracy(const Tri &t, double *phi, long long *keys, cudaStream_t st);
-void shift_signal(const Tri &t, double *phi, long long *keys, cudaStream_t st);
+void remove_degeneracy(const Tri &t, double *phi, long long *keys, cudaStream_t st, const Share &sh = Share());
+void shift_signal(const Tri &t, double *phi, long long *keys, cudaStream_t st, const Share &sh = Share());
 
 // Signal data frame columns (fast_dataframe.cpp:62-88); lam1 is a device array [D]. Any output may be null.
 void output_signal(const Tri &t, LegTables L, const int32_t *nobs, const double *phi, const double *lam1,

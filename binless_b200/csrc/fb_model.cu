@@ -528,6 +528,14 @@ GflSolver &Model::solver(unsigned maxdiag) {
     return *flo_;
 }
 
+// the GPUs of the communicator share the reduction passes (fb_irls.cuh: Share); FB_IRLS_REPLICATED=1 keeps them replicated
+Share Model::share() const {
+    Share s;
+    Comm &c = Comm::get();
+    if (c.active() && !std::getenv("FB_IRLS_REPLICATED")) { s.rank = c.rank(); s.world = c.world(); s.cm = &c; }
+    return s;
+}
+
 void Model::check_interrupt() {
     if (interrupt_cb && interrupt_cb(interrupt_arg)) throw Interrupted("interrupted");
 }
@@ -667,7 +675,7 @@ void Model::run_signal(const fb_params *p, fb_signal_out *out) {
         if (bg) FB_CUDA(cudaMemcpyAsync(tab_old_.p, tab_.p, tab_.n * sizeof(double), cudaMemcpyDeviceToDevice, st_));
         fit_decay(MODE_RESID);
         if (bg) {
-            precision(t_, tables(tab_old_), tables(tab_), phi_.p, phi_.p, scratch_.p, scratch_.p + 8, st_);
+            precision(t_, tables(tab_old_), tables(tab_), phi_.p, phi_.p, scratch_.p, scratch_.p + 8, st_, share());
             kernel_launches += 3;
         } else {
             signal_yw(t_, tables(tab_), alpha_, obs_.p, nobs_.p, phi_.p, 0, phihat_.p, wgt_.p, st_);
@@ -681,10 +689,10 @@ void Model::run_signal(const fb_params *p, fb_signal_out *out) {
                 if (out->solve_iters && n_solves < out->solve_iters_cap) out->solve_iters[n_solves] = it;
                 ++n_solves; iters += it; cell_iters += (int64_t)it * flo.grid().ncells;
                 flo.get_beta_full(phi_new_.p + (size_t)d * nc);
-                center_dataset(nc, nobs_.p + (size_t)d * nc, phi_new_.p + (size_t)d * nc, scratch_.p + 16, st_);
+                center_dataset(nc, nobs_.p + (size_t)d * nc, phi_new_.p + (size_t)d * nc, scratch_.p + 16, st_, share());
                 kernel_launches += 3;
             }
-            precision(t_, tables(tab_), tables(tab_), phi_.p, phi_new_.p, scratch_.p, scratch_.p + 8, st_);
+            precision(t_, tables(tab_), tables(tab_), phi_.p, phi_new_.p, scratch_.p, scratch_.p + 8, st_, share());
             kernel_launches += 3;
             std::swap(phi_.p, phi_new_.p);
         }
@@ -697,8 +705,8 @@ void Model::run_signal(const fb_params *p, fb_signal_out *out) {
         if (converged && step <= bg_steps) { converged = false; bg_steps = step; }
         current_tol_val = std::min(current_tol_val, std::max(tol_val, pabs));
         flo_tol = current_tol_val / 20;
-        if (converged || step == p->nouter) { shift_signal(t_, phi_.p, keys_.p, st_); kernel_launches += 3; }
-        else { remove_degeneracy(t_, phi_.p, keys_.p, st_); kernel_launches += 3; }
+        if (converged || step == p->nouter) { shift_signal(t_, phi_.p, keys_.p, st_, share()); kernel_launches += 3; }
+        else { remove_degeneracy(t_, phi_.p, keys_.p, st_, share()); kernel_launches += 3; }
         fit_expo(MODE_RESID);
         out->nsteps = (int)step;
         if (converged) { if (p->verbose) std::printf("converged\n"); out->converged = 1; break; }
@@ -856,7 +864,7 @@ void Model::eval_cv(const fb_params *p, int nlam, const double *lam2v, unsigned 
         signal_yw(t_, tables(tab_), alpha_, obs_.p, nobs_.p, phi_.p, group, y.p, w.p, st_);
         flo.optimize(y.p, w.p, lam2v[k], p->tol_val / 20.);
         flo.get_beta_full(phi_cv.p);
-        center_dataset(N, nobs_.p, phi_cv.p, scratch_.p + 16, st_);
+        center_dataset(N, nobs_.p, phi_cv.p, scratch_.p + 16, st_, share());
         fb_cv_out &o = outs[k];
         output_signal(t_, tables(tab_), nobs_.p, phi_cv.p, lam1_d.p, nullptr, nullptr, nullptr,
                       o.signal ? sig.p : nullptr, o.binless ? binl.p : nullptr, st_);
@@ -896,7 +904,7 @@ void Model::sweep_lambda(const fb_params *p, int nlam, const double *lam2v, fb_s
             ms_solver += flo.ms_last;
             cell_iters += (int64_t)(steps - 1) * flo.grid().ncells;
             flo.get_beta_full(beta.p);
-            center_dataset(nc, nobs_.p + (size_t)d * nc, beta.p, scratch_.p + 16, st_);
+            center_dataset(nc, nobs_.p + (size_t)d * nc, beta.p, scratch_.p + 16, st_, share());
             patch_labels(n, p->tol_val, beta.p, parent.p, scan.p, labels.p, st_);
             sweep_score(nc, y.p + (size_t)d * nc, w.p + (size_t)d * nc, beta.p, labels.p, lam1[d], p->tol_val, flags.p,
                         partial.p, res.p, st_);
@@ -947,7 +955,7 @@ void Model::cv_score(const fb_params *p, int nlam, const double *lam2v, fb_cv_sc
                 ms_solver += flo.ms_last;
                 cell_iters += (int64_t)(st - 1) * flo.grid().ncells;
                 flo.get_beta_full(beta.p);
-                center_dataset(nc, nobs_.p + (size_t)d * nc, beta.p, scratch_.p + 16, st_);
+                center_dataset(nc, nobs_.p + (size_t)d * nc, beta.p, scratch_.p + 16, st_, share());
                 cv_group_sum(n, g, y.p + (size_t)d * nc, w.p + (size_t)d * nc, beta.p, lam1[d], partial.p, res.p, st_);
                 kernel_launches += 1 + 3 + 2;
                 FB_CUDA(cudaMemcpyAsync(res_h.p, res.p, 2 * sizeof(double), cudaMemcpyDeviceToHost, st_));

@@ -98,6 +98,7 @@ private:
     std::unique_ptr<GflSolver> flo_;                  // kept across calls (structure only; every call starts from reset())
     unsigned flo_maxdiag_ = 0; int flo_comm_ = 1;
     GflSolver &solver(unsigned maxdiag);
+    Share share() const;
     void open_stream();
     void close_stream();
     void ingest_cells(const fb_mat *mat);
