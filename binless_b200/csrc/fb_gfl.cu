@@ -584,12 +584,20 @@ __global__ void k_band_outside_sums(Grid g, int nbins, const double *__restrict_
     }
     if (threadIdx.x == 0) { partial[2 * i] = s_a[0]; partial[2 * i + 1] = s_b[0]; }
 }
-__global__ void k_band_avg(int nrows, const double *__restrict__ partial, double *__restrict__ avg) {
-    if (threadIdx.x == 0 && blockIdx.x == 0) {
-        double a = 0.0, b = 0.0;
-        for (int i = 0; i < nrows; ++i) { a += partial[2 * i]; b += partial[2 * i + 1]; }
-        avg[0] = a / b;
+// the per-row sums in a fixed shape: 1024 threads stride over the rows, then a tree (a single thread walking 50 000 rows
+// took 3.2 ms per solve at chromosome scale)
+__global__ void __launch_bounds__(1024)
+k_band_avg(int nrows, const double *__restrict__ partial, double *__restrict__ avg) {
+    __shared__ double s_a[1024], s_b[1024];
+    double a = 0.0, b = 0.0;
+    for (int i = threadIdx.x; i < nrows; i += 1024) { a += partial[2 * i]; b += partial[2 * i + 1]; }
+    s_a[threadIdx.x] = a; s_b[threadIdx.x] = b;
+    __syncthreads();
+    for (int o = 512; o > 0; o >>= 1) {
+        if ((int)threadIdx.x < o) { s_a[threadIdx.x] += s_a[threadIdx.x + o]; s_b[threadIdx.x] += s_b[threadIdx.x + o]; }
+        __syncthreads();
     }
+    if (threadIdx.x == 0) avg[0] = s_a[0] / s_b[0];
 }
 // beta (clamped at +-50) scattered to the full triangle; outside the band = avg
 __global__ void k_beta_full(Grid g, int nbins, const double *__restrict__ beta, const double *__restrict__ avg,
@@ -1036,7 +1044,7 @@ int GflSolver::optimize(const double *d_y_tri, const double *d_w_tri, double lam
         // the rows of the far region are dealt to the ranks; the per-row sums of the others arrive as x + 0 (exact)
         k_band_outside_sums<<<nbins_, 256, 0, st_>>>(g_, nbins_, d_y_tri, d_w_tri, band_partials_.p, sharded_ ? rank_ : 0, sharded_ ? world_ : 1);
         if (sharded_) Comm::get().allreduce_sum(band_partials_.p, band_partials_.p, 2 * (size_t)nbins_, st_);
-        k_band_avg<<<1, 32, 0, st_>>>(nbins_, band_partials_.p, fillavg_.p);
+        k_band_avg<<<1, 1024, 0, st_>>>(nbins_, band_partials_.p, fillavg_.p);
         kernel_launches += 2;
     }
     FB_CUDA(cudaEventRecord(ev1_, st_));

@@ -271,8 +271,12 @@ k_sum_groups(int nitems, const double *__restrict__ items_g, double *__restrict_
 
 __global__ void __launch_bounds__(EW_THREADS)
 k_signal_yw(Tri t, LegTables L, double alpha, const int32_t *__restrict__ obs, const int32_t *__restrict__ nobs,
-            const double *__restrict__ phi, unsigned group, double *__restrict__ y, double *__restrict__ w) {
+            const double *__restrict__ phi, unsigned group, double *__restrict__ y, double *__restrict__ w,
+            const int sh_rank, const int sh_world, const int md) {
     EW_FOREACH_CELL(t) {
+        // band solves shared between GPUs: beyond the band only the far-region sums need (y, w), and their rows are dealt
+        // to the ranks (k_band_outside_sums reads the same rows)
+        if (off >= md && (i % sh_world) != sh_rank) continue;
         const int64_t idx = rowbase + off;
         const double ph = phi[idx];
         double z, wt;
@@ -766,8 +770,8 @@ void cv_group_sum(int n, int g, const double *phihat, const double *w, const dou
 }
 
 void signal_yw(const Tri &t, LegTables L, double alpha, const int32_t *obs, const int32_t *nobs, const double *phi,
-               unsigned group, double *y, double *w, cudaStream_t st) {
-    k_signal_yw<<<ew_grid(t), EW_THREADS, 0, st>>>(t, L, alpha, obs, nobs, phi, group, y, w);
+               unsigned group, double *y, double *w, cudaStream_t st, const Share &sh, int md) {
+    k_signal_yw<<<ew_grid(t), EW_THREADS, 0, st>>>(t, L, alpha, obs, nobs, phi, group, y, w, sh.rank, sh.world, sh.on() ? md : t.n);
     FB_LAUNCH_CHECK();
 }
 

@@ -89,9 +89,10 @@ constexpr int CV_BLOCKS = 592;
 void cv_group_sum(int n, int g, const double *phihat, const double *w, const double *beta, double lam1, double *partial,
                   double *out2, cudaStream_t st);
 
-// y = z + phi, w (step_signal, fast_binless.ipp:13-23); group = CV hold-out (0 = none)
+// y = z + phi, w (step_signal, fast_binless.ipp:13-23); group = CV hold-out (0 = none). With a Share and a band width md the
+// cells beyond the band are written only on the rows of this rank (the far-region sums of a band solve are all they feed)
 void signal_yw(const Tri &t, LegTables L, double alpha, const int32_t *obs, const int32_t *nobs, const double *phi,
-               unsigned group, double *y, double *w, cudaStream_t st);
+               unsigned group, double *y, double *w, cudaStream_t st, const Share &sh = Share(), int md = 1 << 30);
 
 // beta[d] -= sum(beta*nobs)/sum(nobs) (fast_binless.ipp:33-44); scratch >= 2*1024+2 doubles
 void center_dataset(int64_t ncells, const int32_t *nobs_d, double *beta_d, double *scratch, cudaStream_t st, const Share &sh = Share());

@@ -164,7 +164,7 @@ void Model::alloc_tables() {
     const int64_t n = t_.n, D = t_.D;
     if (!generic_) { tab_b_ = (int)n; tab_d_ = (int)n; }
     const size_t tn = (size_t)tab_b_ + tab_d_ + D;
-    tab_.alloc(tn); tab_old_.alloc(tn); tab_h_.alloc(tn);
+    tab_.alloc(tn); tab_old_.alloc(tn); tab_sig_.alloc(tn); tab_h_.alloc(tn);
     const size_t items = 2 * (size_t)std::max<int64_t>(std::max<int64_t>(n, D), std::max(tab_b_, tab_d_));
     items_.alloc(items); items_h_.alloc(items);
     items_g_.alloc((size_t)LEG_GROUPS * items);
@@ -666,6 +666,7 @@ void Model::run_signal(const fb_params *p, fb_signal_out *out) {
     const std::vector<double> lam2 = broadcast(p->lam2, p->n_lam2, D);
     const std::vector<double> lam1 = broadcast(p->lam1, p->n_lam1, D);
     int64_t n_solves = 0, iters = 0, cell_iters = 0;
+    bool sig_partial = false;
     out->nsteps = 0; out->converged = 0;
     for (unsigned step = 1; step <= p->nouter; ++step) {
         check_interrupt();
@@ -678,7 +679,13 @@ void Model::run_signal(const fb_params *p, fb_signal_out *out) {
             precision(t_, tables(tab_old_), tables(tab_), phi_.p, phi_.p, scratch_.p, scratch_.p + 8, st_, share());
             kernel_launches += 3;
         } else {
-            signal_yw(t_, tables(tab_), alpha_, obs_.p, nobs_.p, phi_.p, 0, phihat_.p, wgt_.p, st_);
+            // band solve shared between GPUs: (phihat, w) beyond the band only on this rank's rows; the full columns are
+            // rebuilt after the loop from the inputs of the last signal step (phi_new_ after the swap, the tables saved here)
+            const Share sh = share();
+            const bool partial = sh.on() && flo.trapeze();
+            signal_yw(t_, tables(tab_), alpha_, obs_.p, nobs_.p, phi_.p, 0, phihat_.p, wgt_.p, st_, partial ? sh : Share(), flo.grid().md);
+            if (partial) FB_CUDA(cudaMemcpyAsync(tab_sig_.p, tab_.p, tab_.n * sizeof(double), cudaMemcpyDeviceToDevice, st_));
+            sig_partial = partial;
             kernel_launches += 1;
             for (int d = 0; d < D; ++d) {
                 g_pt.start();
@@ -710,6 +717,10 @@ void Model::run_signal(const fb_params *p, fb_signal_out *out) {
         fit_expo(MODE_RESID);
         out->nsteps = (int)step;
         if (converged) { if (p->verbose) std::printf("converged\n"); out->converged = 1; break; }
+    }
+    if (sig_partial) {   // the (phihat, weight) columns of the last signal step in full
+        signal_yw(t_, tables(tab_sig_), alpha_, obs_.p, nobs_.p, phi_new_.p, 0, phihat_.p, wgt_.p, st_);
+        kernel_launches += 1;
     }
     kernel_launches += flo.kernel_launches;
     if (p->verbose) std::printf("done\n");

@@ -73,7 +73,7 @@ private:
     std::vector<double> expo_est_, bias_est_;         // Params<Mean>::estimate (mean = 0)
     DecayGam dec_;
     // device leg tables: [brow n | ddiag n | expo D], current and the copy taken before the decay update
-    DevBuf<double> tab_, tab_old_;
+    DevBuf<double> tab_, tab_old_, tab_sig_;          // tab_sig_: the tables of the last signal step (shared band solves)
     PinBuf<double> tab_h_, items_h_, prec_h_;
     DevBuf<double> part_, items_, items_g_, scratch_;   // items_g_: the per-group sums of a leg pass (fb_irls.cuh)
     DevBuf<long long> keys_;
