@@ -51,7 +51,10 @@ k_beta(Grid g, const GflCtl *__restrict__ ctl, const double *__restrict__ y, con
        double *__restrict__ uc, double *__restrict__ beta, double *__restrict__ betaT,
        const int r0, const int r1, const int c0, const int c1) {
     if (ctl->done) return;
-    const int i0 = blockIdx.y * TILE, j0 = blockIdx.x * TILE;
+    // the grid covers the band only: tile column = tile row + blockIdx.x (a full-width grid at chromosome scale launched
+    // 2.4 million CTAs that returned at once: 2.4 ms per iteration at 50 000 bins with a 2000-wide band)
+    const int i0 = blockIdx.y * TILE, j0 = (blockIdx.y + blockIdx.x) * TILE;
+    if (j0 >= g.n) return;
     // tile must intersect the band 0 <= j-i < md
     if (j0 + TILE - 1 < i0 || j0 - (i0 + TILE - 1) >= g.md) return;
     // ... and hold a cell of a chain this rank owns (rows [r0, r1) or columns [c0, c1); everything when not sharded)
@@ -118,7 +121,10 @@ k_beta(Grid g, const GflCtl *__restrict__ ctl, const double *__restrict__ y, con
        double *__restrict__ uc, double *__restrict__ beta, double *__restrict__ betaT,
        const int r0, const int r1, const int c0, const int c1) {
     if (ctl->done) return;
-    const int i0 = blockIdx.y * TILE, j0 = blockIdx.x * TILE;
+    // the grid covers the band only: tile column = tile row + blockIdx.x (a full-width grid at chromosome scale launched
+    // 2.4 million CTAs that returned at once: 2.4 ms per iteration at 50 000 bins with a 2000-wide band)
+    const int i0 = blockIdx.y * TILE, j0 = (blockIdx.y + blockIdx.x) * TILE;
+    if (j0 >= g.n) return;
     // tile must intersect the band 0 <= j-i < md
     if (j0 + TILE - 1 < i0 || j0 - (i0 + TILE - 1) >= g.md) return;
     // ... and hold a cell of a chain this rank owns (rows [r0, r1) or columns [c0, c1); everything when not sharded)
@@ -521,6 +527,26 @@ k_push(Grid g, const GflCtl *__restrict__ ctl, const ShardRegion *__restrict__ r
         }
     }
 }
+// the residual sums of this rank's chains (4 doubles per chain) into every rank's full array: what the all-reduce of the
+// zero-padded arrays produced, without adding anything (3.2 MB took NCCL 4 ms per iteration on 8 GPUs at 50 000 bins)
+__global__ void __launch_bounds__(256)
+k_push_partials(const GflCtl *__restrict__ ctl, const int *__restrict__ list, int nlist, const double *__restrict__ partials,
+                double *__restrict__ all_local, double *const *__restrict__ peer, int npeers) {
+    if (ctl->idle) return;
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= nlist) return;
+    const int q = list[k];
+    const double2 a = *reinterpret_cast<const double2 *>(partials + 4 * (size_t)q);
+    const double2 b = *reinterpret_cast<const double2 *>(partials + 4 * (size_t)q + 2);
+    *reinterpret_cast<double2 *>(all_local + 4 * (size_t)q) = a;
+    *reinterpret_cast<double2 *>(all_local + 4 * (size_t)q + 2) = b;
+    for (int p = 0; p < npeers; ++p) {
+        double *dst = peer[p];
+        *reinterpret_cast<double2 *>(dst + 4 * (size_t)q) = a;
+        *reinterpret_cast<double2 *>(dst + 4 * (size_t)q + 2) = b;
+    }
+}
+
 // the duals of the cells whose chains another rank owns are zero here (their z holds z - u of the owner)
 template <int DIR>
 __global__ void __launch_bounds__(256)
@@ -760,7 +786,7 @@ void GflSolver::setup_shard() {
 // fall back to the packed ncclSend / ncclRecv exchange: the decision is all-reduced.
 void GflSolver::setup_p2p() {
     Comm &cm = Comm::get();
-    struct Info { cudaIpcMemHandle_t hr, hc; unsigned long long pr, pc; long long pid, dev; };
+    struct Info { cudaIpcMemHandle_t hr, hc, hp; unsigned long long pr, pc, pp; long long pid, dev; };
     static_assert(sizeof(Info) % sizeof(double) == 0, "Info is sent as doubles");
     constexpr int ND = sizeof(Info) / sizeof(double);
     const char *env = std::getenv("FB_SHARD_P2P");
@@ -769,8 +795,10 @@ void GflSolver::setup_p2p() {
     std::memset(info.data(), 0, info.size() * sizeof(Info));
     Info &me = info[rank_];
     int dev = 0; cudaGetDevice(&dev);
-    me.pr = (unsigned long long)zr_.p; me.pc = (unsigned long long)zc_.p; me.pid = (long long)getpid(); me.dev = dev;
-    if (ok && (cudaIpcGetMemHandle(&me.hr, zr_.p) != cudaSuccess || cudaIpcGetMemHandle(&me.hc, zc_.p) != cudaSuccess)) { cudaGetLastError(); ok = false; }
+    me.pr = (unsigned long long)zr_.p; me.pc = (unsigned long long)zc_.p; me.pp = (unsigned long long)partials_all_.p;
+    me.pid = (long long)getpid(); me.dev = dev;
+    if (ok && (cudaIpcGetMemHandle(&me.hr, zr_.p) != cudaSuccess || cudaIpcGetMemHandle(&me.hc, zc_.p) != cudaSuccess ||
+               cudaIpcGetMemHandle(&me.hp, partials_all_.p) != cudaSuccess)) { cudaGetLastError(); ok = false; }
     DevBuf<double> buf((size_t)ND * world_);
     FB_CUDA(cudaMemcpyAsync(buf.p + (size_t)ND * rank_, &me, sizeof(Info), cudaMemcpyHostToDevice, st_));
     cm.group_start();
@@ -778,24 +806,25 @@ void GflSolver::setup_p2p() {
     cm.group_end();
     FB_CUDA(cudaMemcpyAsync(info.data(), buf.p, info.size() * sizeof(Info), cudaMemcpyDeviceToHost, st_));
     FB_CUDA(cudaStreamSynchronize(st_));
-    std::vector<double *> pr, pc;
+    std::vector<double *> pr, pc, pq;
     for (int p = 0; p < world_ && ok; ++p) {
         if (p == rank_) continue;
-        double *r = nullptr, *c = nullptr;
+        double *r = nullptr, *c = nullptr, *q = nullptr;
         if (info[p].pid == me.pid) {     // same process (fb_create_multi): one address space
             int can = 0;
             if (cudaDeviceCanAccessPeer(&can, dev, (int)info[p].dev) != cudaSuccess || !can) { cudaGetLastError(); ok = false; break; }
             const cudaError_t e = cudaDeviceEnablePeerAccess((int)info[p].dev, 0);
             if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) { cudaGetLastError(); ok = false; break; }
             cudaGetLastError();
-            r = (double *)info[p].pr; c = (double *)info[p].pc;
+            r = (double *)info[p].pr; c = (double *)info[p].pc; q = (double *)info[p].pp;
         } else {
             void *a = cm.ipc_open(info[p].hr), *b = a ? cm.ipc_open(info[p].hc) : nullptr;   // kept open by the communicator
-            if (!a || !b) { ok = false; break; }
+            void *d = (a && b) ? cm.ipc_open(info[p].hp) : nullptr;
+            if (!a || !b || !d) { ok = false; break; }
             p2p_ipc_ = true;
-            r = (double *)a; c = (double *)b;
+            r = (double *)a; c = (double *)b; q = (double *)d;
         }
-        pr.push_back(r); pc.push_back(c);
+        pr.push_back(r); pc.push_back(c); pq.push_back(q);
     }
     // agree: the sum of the failure flags over the ranks
     bar_.alloc(4);
@@ -810,9 +839,11 @@ void GflSolver::setup_p2p() {
                      tot[0] != 0.0 ? "packed ncclSend / ncclRecv" : (p2p_ipc_ ? "peer stores (CUDA IPC)" : "peer stores (same process)"));
     if (tot[0] != 0.0) { teardown_p2p(); p2p_ = false; return; }
     peer_zr_.alloc(std::max<size_t>(1, pr.size())); peer_zc_.alloc(std::max<size_t>(1, pc.size()));
+    peer_part_.alloc(std::max<size_t>(1, pq.size()));
     if (!pr.empty()) {
         FB_CUDA(cudaMemcpy(peer_zr_.p, pr.data(), pr.size() * sizeof(double *), cudaMemcpyHostToDevice));
         FB_CUDA(cudaMemcpy(peer_zc_.p, pc.data(), pc.size() * sizeof(double *), cudaMemcpyHostToDevice));
+        FB_CUDA(cudaMemcpy(peer_part_.p, pq.data(), pq.size() * sizeof(double *), cudaMemcpyHostToDevice));
     }
     p2p_ = true;
 }
@@ -892,11 +923,8 @@ void GflSolver::allgather_cols(double *a) {
 
 GflSolver::~GflSolver() {
     cudaStreamSynchronize(st_); // buffers go back to the block cache only when nothing uses them any more
-    if (sharded_ && p2p_) {
-        // no peer may still be storing into these arrays when they go back to the cache (and no handle stays open)
-        try { Comm::get().allreduce_sum(bar_.p, bar_.p + 2, 1, st_); cudaStreamSynchronize(st_); } catch (...) {}
-        teardown_p2p();
-    }
+    // (peer stores: every exchange ends with a barrier all-reduce that this rank's stream has passed, so no peer is still
+    // storing into these arrays; a collective in a destructor would hang the survivors of a failed rank)
     if (shard_timing_ && tcount_) {
         static const char *nm_nccl[7] = {"k_beta", "k_prox", "allreduce", "k_ctl", "pack", "send/recv", "unpack"};
         static const char *nm_p2p[7] = {"k_beta", "k_prox", "allreduce", "k_ctl", "-", "push (peer stores)", "barrier"};
@@ -924,7 +952,8 @@ void GflSolver::reset() {
 }
 
 void GflSolver::launch_iteration(const double *y, const double *w, bool in_graph) {
-    dim3 tb(TILE, 8), tg((g_.n + TILE - 1) / TILE, (g_.n + TILE - 1) / TILE);
+    const int nt = (g_.n + TILE - 1) / TILE;
+    dim3 tb(TILE, 8), tg((unsigned)std::min(nt, (g_.md + TILE - 2) / TILE + 2), (unsigned)nt);   // tile columns that can touch the band
     tmark(0);
     k_beta<<<tg, tb, 0, st_>>>(g_, ctl_.p, y, w, zr_.p, ur_.p, zc_.p, uc_.p, beta_.p, betaT_.p, r0_, r1_, c0_, c1_);
     tmark(1);
@@ -947,7 +976,13 @@ void GflSolver::launch_iteration(const double *y, const double *w, bool in_graph
     // sharded: the residual sums of every chain on every rank (exactly one rank contributes a non-zero term per
     // slot, so the sum is exact and k_ctl reduces the same numbers in the same order everywhere)
     tmark(2);
-    if (sharded_) Comm::get().allreduce_sum(partials_.p, partials_all_.p, 2 * (size_t)n_partials_, st_);
+    if (sharded_ && p2p_) {
+        // every rank stores the sums of its own chains into everybody's array (peer stores), then a scalar all-reduce as
+        // the barrier: the same numbers in the same slots as the all-reduce of the zero-padded arrays, nothing added
+        if (n_list_) k_push_partials<<<(n_list_ + 255) / 256, 256, 0, st_>>>(ctl_.p, chain_list_.p, n_list_, partials_.p, partials_all_.p,
+                                                                          peer_part_.p, world_ - 1);
+        Comm::get().allreduce_sum(bar_.p, bar_.p + 2, 1, st_);
+    } else if (sharded_) Comm::get().allreduce_sum(partials_.p, partials_all_.p, 2 * (size_t)n_partials_, st_);
     tmark(3);
     const double *parts = sharded_ ? partials_all_.p : partials_.p;
     if (fold.on) { tmark(4); return; }
