@@ -547,6 +547,15 @@ k_push_partials(const GflCtl *__restrict__ ctl, const int *__restrict__ list, in
     }
 }
 
+// the solution of this rank's row block into every peer's beta (the all-gather at the end of a solve, by peer stores)
+__global__ void __launch_bounds__(256)
+k_push_rows(const double *__restrict__ src, int64_t b, int64_t e, double *const *__restrict__ peer, int npeers) {
+    for (int64_t i = b + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < e; i += (int64_t)gridDim.x * blockDim.x) {
+        const double v = src[i];
+        for (int p = 0; p < npeers; ++p) peer[p][i] = v;
+    }
+}
+
 // the duals of the cells whose chains another rank owns are zero here (their z holds z - u of the owner)
 template <int DIR>
 __global__ void __launch_bounds__(256)
@@ -786,7 +795,7 @@ void GflSolver::setup_shard() {
 // fall back to the packed ncclSend / ncclRecv exchange: the decision is all-reduced.
 void GflSolver::setup_p2p() {
     Comm &cm = Comm::get();
-    struct Info { cudaIpcMemHandle_t hr, hc, hp; unsigned long long pr, pc, pp; long long pid, dev; };
+    struct Info { cudaIpcMemHandle_t hr, hc, hp, hb; unsigned long long pr, pc, pp, pb; long long pid, dev; };
     static_assert(sizeof(Info) % sizeof(double) == 0, "Info is sent as doubles");
     constexpr int ND = sizeof(Info) / sizeof(double);
     const char *env = std::getenv("FB_SHARD_P2P");
@@ -796,9 +805,12 @@ void GflSolver::setup_p2p() {
     Info &me = info[rank_];
     int dev = 0; cudaGetDevice(&dev);
     me.pr = (unsigned long long)zr_.p; me.pc = (unsigned long long)zc_.p; me.pp = (unsigned long long)partials_all_.p;
+    me.pb = (unsigned long long)beta_.p;
     me.pid = (long long)getpid(); me.dev = dev;
     if (ok && (cudaIpcGetMemHandle(&me.hr, zr_.p) != cudaSuccess || cudaIpcGetMemHandle(&me.hc, zc_.p) != cudaSuccess ||
-               cudaIpcGetMemHandle(&me.hp, partials_all_.p) != cudaSuccess)) { cudaGetLastError(); ok = false; }
+               cudaIpcGetMemHandle(&me.hp, partials_all_.p) != cudaSuccess || cudaIpcGetMemHandle(&me.hb, beta_.p) != cudaSuccess)) {
+        cudaGetLastError(); ok = false;
+    }
     DevBuf<double> buf((size_t)ND * world_);
     FB_CUDA(cudaMemcpyAsync(buf.p + (size_t)ND * rank_, &me, sizeof(Info), cudaMemcpyHostToDevice, st_));
     cm.group_start();
@@ -806,25 +818,25 @@ void GflSolver::setup_p2p() {
     cm.group_end();
     FB_CUDA(cudaMemcpyAsync(info.data(), buf.p, info.size() * sizeof(Info), cudaMemcpyDeviceToHost, st_));
     FB_CUDA(cudaStreamSynchronize(st_));
-    std::vector<double *> pr, pc, pq;
+    std::vector<double *> pr, pc, pq, pbeta;
     for (int p = 0; p < world_ && ok; ++p) {
         if (p == rank_) continue;
-        double *r = nullptr, *c = nullptr, *q = nullptr;
+        double *r = nullptr, *c = nullptr, *q = nullptr, *bt = nullptr;
         if (info[p].pid == me.pid) {     // same process (fb_create_multi): one address space
             int can = 0;
             if (cudaDeviceCanAccessPeer(&can, dev, (int)info[p].dev) != cudaSuccess || !can) { cudaGetLastError(); ok = false; break; }
             const cudaError_t e = cudaDeviceEnablePeerAccess((int)info[p].dev, 0);
             if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) { cudaGetLastError(); ok = false; break; }
             cudaGetLastError();
-            r = (double *)info[p].pr; c = (double *)info[p].pc; q = (double *)info[p].pp;
+            r = (double *)info[p].pr; c = (double *)info[p].pc; q = (double *)info[p].pp; bt = (double *)info[p].pb;
         } else {
             void *a = cm.ipc_open(info[p].hr), *b = a ? cm.ipc_open(info[p].hc) : nullptr;   // kept open by the communicator
-            void *d = (a && b) ? cm.ipc_open(info[p].hp) : nullptr;
-            if (!a || !b || !d) { ok = false; break; }
+            void *d = (a && b) ? cm.ipc_open(info[p].hp) : nullptr, *e = d ? cm.ipc_open(info[p].hb) : nullptr;
+            if (!a || !b || !d || !e) { ok = false; break; }
             p2p_ipc_ = true;
-            r = (double *)a; c = (double *)b; q = (double *)d;
+            r = (double *)a; c = (double *)b; q = (double *)d; bt = (double *)e;
         }
-        pr.push_back(r); pc.push_back(c); pq.push_back(q);
+        pr.push_back(r); pc.push_back(c); pq.push_back(q); pbeta.push_back(bt);
     }
     // agree: the sum of the failure flags over the ranks
     bar_.alloc(4);
@@ -839,11 +851,12 @@ void GflSolver::setup_p2p() {
                      tot[0] != 0.0 ? "packed ncclSend / ncclRecv" : (p2p_ipc_ ? "peer stores (CUDA IPC)" : "peer stores (same process)"));
     if (tot[0] != 0.0) { teardown_p2p(); p2p_ = false; return; }
     peer_zr_.alloc(std::max<size_t>(1, pr.size())); peer_zc_.alloc(std::max<size_t>(1, pc.size()));
-    peer_part_.alloc(std::max<size_t>(1, pq.size()));
+    peer_part_.alloc(std::max<size_t>(1, pq.size())); peer_beta_.alloc(std::max<size_t>(1, pbeta.size()));
     if (!pr.empty()) {
         FB_CUDA(cudaMemcpy(peer_zr_.p, pr.data(), pr.size() * sizeof(double *), cudaMemcpyHostToDevice));
         FB_CUDA(cudaMemcpy(peer_zc_.p, pc.data(), pc.size() * sizeof(double *), cudaMemcpyHostToDevice));
         FB_CUDA(cudaMemcpy(peer_part_.p, pq.data(), pq.size() * sizeof(double *), cudaMemcpyHostToDevice));
+        FB_CUDA(cudaMemcpy(peer_beta_.p, pbeta.data(), pbeta.size() * sizeof(double *), cudaMemcpyHostToDevice));
     }
     p2p_ = true;
 }
@@ -1074,7 +1087,12 @@ int GflSolver::optimize(const double *d_y_tri, const double *d_w_tri, double lam
     } else last_steps = 1;
     counter += last_steps;
     cold_ = false;
-    if (sharded_) allgather_rows(beta_.p);   // every rank continues with the whole solution
+    if (sharded_ && p2p_) {                  // every rank continues with the whole solution: row blocks by peer stores + barrier
+        const int64_t b = g_.rm_row_start(row_begin_[rank_]), e = g_.rm_row_start(row_begin_[rank_ + 1]);
+        if (e > b) k_push_rows<<<(unsigned)std::min<int64_t>(4 * 148, (e - b + 255) / 256), 256, 0, st_>>>(beta_.p, b, e, peer_beta_.p, world_ - 1);
+        Comm::get().allreduce_sum(bar_.p, bar_.p + 2, 1, st_);
+        kernel_launches += 1;
+    } else if (sharded_) allgather_rows(beta_.p);
     if (trapeze_) { // average of the far region (fill_triangle)
         // the rows of the far region are dealt to the ranks; the per-row sums of the others arrive as x + 0 (exact)
         k_band_outside_sums<<<nbins_, 256, 0, st_>>>(g_, nbins_, d_y_tri, d_w_tri, band_partials_.p, sharded_ ? rank_ : 0, sharded_ ? world_ : 1);

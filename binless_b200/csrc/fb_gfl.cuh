@@ -142,7 +142,7 @@ private:
     // pack / ncclSend / ncclRecv / unpack); peers in other processes are reached through CUDA IPC handles, peers in this
     // process (fb_create_multi) through plain pointers. One scalar all-reduce after the stores is the barrier.
     bool p2p_ = false;
-    DevBuf<double *> peer_zr_, peer_zc_, peer_part_;   // per exchange partner (region order): its zr / zc / partials_all_
+    DevBuf<double *> peer_zr_, peer_zc_, peer_part_, peer_beta_;   // per exchange partner (region order): its zr / zc / partials_all_
     bool p2p_ipc_ = false;
     DevBuf<double> bar_;
     void setup_p2p();
