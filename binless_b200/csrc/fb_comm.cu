@@ -20,9 +20,10 @@ using fn_recv = int (*)(void *, size_t, int, int, void *, cudaStream_t);
 using fn_allreduce = int (*)(const void *, void *, size_t, int, int, void *, cudaStream_t);
 using fn_bcast = int (*)(const void *, void *, size_t, int, int, void *, cudaStream_t);
 using fn_errstr = const char *(*)(int);
-enum { F_UID, F_INIT, F_DESTROY, F_GSTART, F_GEND, F_SEND, F_RECV, F_ALLREDUCE, F_BCAST, F_ERRSTR };
+using fn_allgather = int (*)(const void *, void *, size_t, int, void *, cudaStream_t);
+enum { F_UID, F_INIT, F_DESTROY, F_GSTART, F_GEND, F_SEND, F_RECV, F_ALLREDUCE, F_BCAST, F_ALLGATHER, F_ERRSTR };
 const char *kNames[] = {"ncclGetUniqueId", "ncclCommInitRank", "ncclCommDestroy", "ncclGroupStart", "ncclGroupEnd",
-                        "ncclSend", "ncclRecv", "ncclAllReduce", "ncclBroadcast", "ncclGetErrorString"};
+                        "ncclSend", "ncclRecv", "ncclAllReduce", "ncclBroadcast", "ncclAllGather", "ncclGetErrorString"};
 } // namespace
 
 #define FB_NCCL(call)                                                                                       \
@@ -123,6 +124,10 @@ void Comm::allreduce_sum(const double *src, double *dst, size_t n, cudaStream_t 
 void Comm::allreduce_i64(long long *buf, size_t n, bool take_max, cudaStream_t s) {
     need();
     FB_NCCL(reinterpret_cast<fn_allreduce>(fn_[F_ALLREDUCE])(buf, buf, n, kNcclInt64, take_max ? kNcclMax : kNcclMin, comm_, s));
+}
+void Comm::allgather(double *buf, size_t n_per_rank, cudaStream_t s) {
+    need();
+    FB_NCCL(reinterpret_cast<fn_allgather>(fn_[F_ALLGATHER])(buf + (size_t)rank_ * n_per_rank, buf, n_per_rank, kNcclFloat64, comm_, s));
 }
 void Comm::bcast(double *p, size_t n, int root, cudaStream_t s) {
     need();

@@ -41,6 +41,7 @@ public:
     void allreduce_sum(const double *src, double *dst, size_t n, cudaStream_t s);
     void bcast(double *p, size_t n, int root, cudaStream_t s);
     void allreduce_i64(long long *buf, size_t n, bool take_max, cudaStream_t s);   // in place; exact in any order
+    void allgather(double *buf, size_t n_per_rank, cudaStream_t s);                // in place: rank r's part at buf + r * n_per_rank
     // CUDA IPC mapping of a peer's allocation, kept for the life of the communicator (opening one costs tens of
     // milliseconds; the solver of every solve asks for the same blocks again); nullptr when it cannot be opened
     void *ipc_open(const cudaIpcMemHandle_t &h);
@@ -50,7 +51,7 @@ private:
     void load();
     void *lib_ = nullptr, *comm_ = nullptr;
     int rank_ = 0, world_ = 1;
-    void *fn_[12] = {};
+    void *fn_[16] = {};
 };
 
 } // namespace fb

@@ -634,6 +634,59 @@ k_band_avg(int nrows, const double *__restrict__ partial, double *__restrict__ a
     }
     if (threadIdx.x == 0) avg[0] = s_a[0] / s_b[0];
 }
+// Centring of a band solution (step_signal, fast_binless.ipp:33-44: beta -= sum(beta nobs) / sum(nobs)) without a pass over
+// the far region: there beta is one value v, so sum(beta nobs) = sum_band clamp(beta) nobs + v (sum(nobs) - sum_band nobs).
+// Per (row, quarter) partial sums over the band, a fixed-shape final sum, then ONE pass writes clamp(beta | v) - centre.
+__global__ void __launch_bounds__(256)
+k_band_center_partial(Grid g, int nbins, const double *__restrict__ beta, const int32_t *__restrict__ nobs_tri, double clampv,
+                      double *__restrict__ partial) {
+    __shared__ double s_a[256], s_b[256];
+    const int i = blockIdx.y;
+    const int len = g.row_len(i);
+    const int64_t src = g.rm_row_start(i), tri = rm_start(i, nbins);
+    double a = 0.0, b = 0.0;
+    for (int d = blockIdx.x * blockDim.x + threadIdx.x; d < len; d += gridDim.x * blockDim.x) {
+        const double no = (double)nobs_tri[tri + d];
+        a += fmin(clampv, fmax(-clampv, beta[src + d])) * no; b += no;
+    }
+    s_a[threadIdx.x] = a; s_b[threadIdx.x] = b;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+        if ((int)threadIdx.x < o) { s_a[threadIdx.x] += s_a[threadIdx.x + o]; s_b[threadIdx.x] += s_b[threadIdx.x + o]; }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) { const int64_t q = (int64_t)i * gridDim.x + blockIdx.x; partial[2 * q] = s_a[0]; partial[2 * q + 1] = s_b[0]; }
+}
+__global__ void __launch_bounds__(1024)
+k_band_center_final(int64_t npart, const double *__restrict__ partial, const double *__restrict__ fill, double clampv, double nobs_total,
+                    double *__restrict__ centre) {
+    __shared__ double s_a[1024], s_b[1024];
+    double a = 0.0, b = 0.0;
+    for (int64_t q = threadIdx.x; q < npart; q += 1024) { a += partial[2 * q]; b += partial[2 * q + 1]; }
+    s_a[threadIdx.x] = a; s_b[threadIdx.x] = b;
+    __syncthreads();
+    for (int o = 512; o > 0; o >>= 1) {
+        if ((int)threadIdx.x < o) { s_a[threadIdx.x] += s_a[threadIdx.x + o]; s_b[threadIdx.x] += s_b[threadIdx.x + o]; }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        const double v = fmin(clampv, fmax(-clampv, fill[0]));
+        centre[0] = (s_a[0] + v * (nobs_total - s_b[0])) / nobs_total;
+    }
+}
+__global__ void k_beta_full_centered(Grid g, int nbins, const double *__restrict__ beta, const double *__restrict__ avg,
+                                     const double *__restrict__ centre, double clampv, double *__restrict__ out) {
+    const int i = blockIdx.y;
+    const int len = g.row_len(i);
+    const int64_t dst = rm_start(i, nbins), src = g.rm_row_start(i);
+    const double c = centre[0];
+    for (int d = blockIdx.x * blockDim.x + threadIdx.x; i + d < nbins; d += gridDim.x * blockDim.x) {
+        double v = (d < len) ? beta[src + d] : avg[0];
+        v = fmin(clampv, fmax(-clampv, v));
+        out[dst + d] = v - c;
+    }
+}
+
 // beta (clamped at +-50) scattered to the full triangle; outside the band = avg
 __global__ void k_beta_full(Grid g, int nbins, const double *__restrict__ beta, const double *__restrict__ avg,
                             double clampv, double *__restrict__ out) {
@@ -1115,6 +1168,18 @@ void GflSolver::get_beta_full(double *d_out_tri) {
     dim3 gg(4, nbins_);
     k_beta_full<<<gg, 256, 0, st_>>>(g_, nbins_, beta_.p, trapeze_ ? fillavg_.p : beta_.p, 50.0, d_out_tri);
     kernel_launches += 1;
+    FB_LAUNCH_CHECK();
+}
+
+// get() and the centring of step_signal in one pass (band solves only; nobs_total = sum of nobs over the dataset, exact)
+void GflSolver::get_beta_full_centered(double *d_out_tri, const int32_t *d_nobs_tri, double nobs_total) {
+    if (!trapeze_) throw StateError("get_beta_full_centered is for band solves");
+    if (!center_partials_.p) { center_partials_.alloc(2 * (size_t)4 * nbins_); center_val_.alloc(1); }
+    dim3 gg(4, nbins_);
+    k_band_center_partial<<<gg, 256, 0, st_>>>(g_, nbins_, beta_.p, d_nobs_tri, 50.0, center_partials_.p);
+    k_band_center_final<<<1, 1024, 0, st_>>>((int64_t)4 * nbins_, center_partials_.p, fillavg_.p, 50.0, nobs_total, center_val_.p);
+    k_beta_full_centered<<<gg, 256, 0, st_>>>(g_, nbins_, beta_.p, fillavg_.p, center_val_.p, 50.0, d_out_tri);
+    kernel_launches += 3;
     FB_LAUNCH_CHECK();
 }
 

@@ -94,6 +94,8 @@ public:
     // clamp(+-50) of the solution scattered to the full packed triangle
     // (FusedLassoGaussianEstimator::get + fill_triangle); out has n(n+1)/2 entries
     void get_beta_full(double *d_out_tri);
+    // band solves: the same with the nobs-weighted mean of the result subtracted (step_signal's centring) in the same pass
+    void get_beta_full_centered(double *d_out_tri, const int32_t *d_nobs_tri, double nobs_total);
     // state import/export in the reference's trail-slot order
     void export_state(double *h_beta, double *h_z, double *h_u) ;
     void import_state(const double *h_beta, const double *h_z, const double *h_u);
@@ -115,7 +117,7 @@ private:
     bool trapeze_;
     cudaStream_t st_;
     DevBuf<double> beta_, betaT_, zr_, ur_, zc_, uc_, yband_, wband_, fillavg_;
-    DevBuf<double> partials_, partials_all_, band_partials_;
+    DevBuf<double> partials_, partials_all_, band_partials_, center_partials_, center_val_;
     // trail-block sharding over the ranks of fb::Comm (inactive: one rank owns every chain)
     bool sharded_ = false;
     int rank_ = 0, world_ = 1;

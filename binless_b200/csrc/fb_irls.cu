@@ -174,6 +174,8 @@ k_leg_pass(Tri t, LegTables L, double alpha, const int32_t *__restrict__ obs, co
 // sums in order. One GPU computes every group itself; `world` GPUs (world divides LEG_GROUPS) compute the groups
 // g mod world == rank each, all-gather the group sums and form the same level-2 sum: bit-identical results.
 __device__ __forceinline__ bool group_is_mine(int g, int grp_rank, int grp_world) { return (g % grp_world) == grp_rank; }
+// where the sums of group g live: the groups of one rank side by side, so that ONE all-gather collects everything
+__host__ __device__ __forceinline__ int group_slot(int g, int grp_world) { return (g % grp_world) * (LEG_GROUPS / grp_world) + g / grp_world; }
 
 __global__ void __launch_bounds__(256)
 k_fin_expo(Tri t, int ntI, int ntJ, const double *__restrict__ part, double *__restrict__ items_g, int grp_rank, int grp_world) {
@@ -189,7 +191,8 @@ k_fin_expo(Tri t, int ntI, int ntJ, const double *__restrict__ part, double *__r
         a += part[p]; b += part[p + 1];
     }
     a = block_sum(a, s_red[0]); b = block_sum(b, s_red[1]);
-    if (threadIdx.x == 0) { items_g[((int64_t)g * t.D + d) * 2] = a; items_g[((int64_t)g * t.D + d) * 2 + 1] = b; }
+    const int64_t o = ((int64_t)group_slot(g, grp_world) * t.D + d) * 2;
+    if (threadIdx.x == 0) { items_g[o] = a; items_g[o + 1] = b; }
 }
 
 // one warp per (bin, group): the row partials (by tile column; they all come from the tile row of the bin) and the
@@ -216,7 +219,8 @@ k_fin_bias(Tri t, int ntI, int ntJ, const double *__restrict__ part, double *__r
         a += v.x; b += v.y;
     }
     a = warp_sum(a); b = warp_sum(b);
-    if (lane == 0) { items_g[((int64_t)g * n + r) * 2] = a; items_g[((int64_t)g * n + r) * 2 + 1] = b; }
+    const int64_t o = ((int64_t)group_slot(g, grp_world) * n + r) * 2;
+    if (lane == 0) { items_g[o] = a; items_g[o + 1] = b; }
 }
 
 // one warp per (diagonal, group)
@@ -245,17 +249,18 @@ k_fin_decay(Tri t, int ntI, int ntJ, const double *__restrict__ part, double *__
         }
     }
     a = warp_sum(a); b = warp_sum(b);
-    if (lane == 0) { items_g[((int64_t)g * t.n + k) * 2] = a; items_g[((int64_t)g * t.n + k) * 2 + 1] = b; }
+    const int64_t o = ((int64_t)group_slot(g, grp_world) * t.n + k) * 2;
+    if (lane == 0) { items_g[o] = a; items_g[o + 1] = b; }
 }
 
 // level 2: the group sums in order
 __global__ void __launch_bounds__(256)
-k_sum_groups(int nitems, const double *__restrict__ items_g, double *__restrict__ items) {
+k_sum_groups(int nitems, const double *__restrict__ items_g, double *__restrict__ items, int grp_world) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= 2 * nitems) return;
     double v = 0.0;
 #pragma unroll
-    for (int g = 0; g < LEG_GROUPS; ++g) v += items_g[(int64_t)g * 2 * nitems + i];
+    for (int g = 0; g < LEG_GROUPS; ++g) v += items_g[(int64_t)group_slot(g, grp_world) * 2 * nitems + i];
     items[i] = v;
 }
 
@@ -739,15 +744,15 @@ void leg_pass_groups(int leg, int mode, const Tri &t, LegTables L, double alpha,
     FB_LAUNCH_CHECK();
 }
 
-void leg_pass_combine(int nitems, const double *items_g, double *items, cudaStream_t st) {
-    k_sum_groups<<<(2 * nitems + 255) / 256, 256, 0, st>>>(nitems, items_g, items);
+void leg_pass_combine(int nitems, const double *items_g, double *items, int grp_world, cudaStream_t st) {
+    k_sum_groups<<<(2 * nitems + 255) / 256, 256, 0, st>>>(nitems, items_g, items, grp_world);
     FB_LAUNCH_CHECK();
 }
 
 void leg_pass(int leg, int mode, const Tri &t, LegTables L, double alpha, const int32_t *obs, const int32_t *nobs,
               const double *phi, double *part, double *items_g, double *items, cudaStream_t st) {
     leg_pass_groups(leg, mode, t, L, alpha, obs, nobs, phi, part, items_g, 0, 1, st);
-    leg_pass_combine(leg == LEG_EXPO ? t.D : t.n, items_g, items, st);
+    leg_pass_combine(leg == LEG_EXPO ? t.D : t.n, items_g, items, 1, st);
 }
 
 void leg_pass_cells(int mode, const Tri &t, LegTables L, double alpha, const int32_t *obs, const int32_t *nobs, const double *phi,

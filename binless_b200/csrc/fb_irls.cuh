@@ -74,7 +74,7 @@ size_t leg_part_doubles(const Tri &t);
 constexpr int LEG_GROUPS = 8;
 void leg_pass_groups(int leg, int mode, const Tri &t, LegTables L, double alpha, const int32_t *obs, const int32_t *nobs,
                      const double *phi, double *part, double *items_g, int grp_rank, int grp_world, cudaStream_t st);
-void leg_pass_combine(int nitems, const double *items_g, double *items, cudaStream_t st);
+void leg_pass_combine(int nitems, const double *items_g, double *items, int grp_world, cudaStream_t st);
 void leg_pass(int leg, int mode, const Tri &t, LegTables L, double alpha, const int32_t *obs, const int32_t *nobs,
               const double *phi, double *part, double *items_g, double *items, cudaStream_t st);
 

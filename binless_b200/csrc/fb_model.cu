@@ -436,12 +436,8 @@ void Model::leg_sums(int leg, int mode, std::vector<double> &a, std::vector<doub
     const int nit = leg == LEG_EXPO ? t_.D : t_.n;
     leg_pass_groups(leg, mode, t_, tables(tab_), alpha_, obs_.p, nobs_.p, phi_.p, part_.p, items_g_.p, shared ? cm.rank() : 0,
                     shared ? cm.world() : 1, st_);
-    if (shared) {
-        cm.group_start();
-        for (int g = 0; g < LEG_GROUPS; ++g) cm.bcast(items_g_.p + (size_t)g * 2 * nit, 2 * (size_t)nit, g % cm.world(), st_);
-        cm.group_end();
-    }
-    leg_pass_combine(nit, items_g_.p, items_.p, st_);
+    if (shared) cm.allgather(items_g_.p, (size_t)(LEG_GROUPS / cm.world()) * 2 * nit, st_);   // a rank's groups lie side by side
+    leg_pass_combine(nit, items_g_.p, items_.p, shared ? cm.world() : 1, st_);
     kernel_launches += 1;
     const int nitems = leg == LEG_EXPO ? t_.D : t_.n;
     FB_CUDA(cudaMemcpyAsync(items_h_.p, items_.p, 2 * (size_t)nitems * sizeof(double), cudaMemcpyDeviceToHost, st_));
@@ -695,9 +691,13 @@ void Model::run_signal(const fb_params *p, fb_signal_out *out) {
                 const int it = steps - 1;
                 if (out->solve_iters && n_solves < out->solve_iters_cap) out->solve_iters[n_solves] = it;
                 ++n_solves; iters += it; cell_iters += (int64_t)it * flo.grid().ncells;
-                flo.get_beta_full(phi_new_.p + (size_t)d * nc);
-                center_dataset(nc, nobs_.p + (size_t)d * nc, phi_new_.p + (size_t)d * nc, scratch_.p + 16, st_, share());
-                kernel_launches += 3;
+                if (flo.trapeze()) {   // band solve: scatter and centring in one pass (the far region is one value)
+                    flo.get_beta_full_centered(phi_new_.p + (size_t)d * nc, nobs_.p + (size_t)d * nc, expo_nobs_[d]);
+                } else {
+                    flo.get_beta_full(phi_new_.p + (size_t)d * nc);
+                    center_dataset(nc, nobs_.p + (size_t)d * nc, phi_new_.p + (size_t)d * nc, scratch_.p + 16, st_, share());
+                    kernel_launches += 3;
+                }
             }
             precision(t_, tables(tab_), tables(tab_), phi_.p, phi_new_.p, scratch_.p, scratch_.p + 8, st_, share());
             kernel_launches += 3;
