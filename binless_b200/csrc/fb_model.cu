@@ -429,7 +429,7 @@ void Model::leg_sums(int leg, int mode, std::vector<double> &a, std::vector<doub
         return;
     }
     // IRLS legs shared between the GPUs of the communicator: every rank sums the tile rows of its groups, the group sums
-    // are gathered (one small broadcast per group from its owner), and everybody adds the groups in the same order: the
+    // are gathered (one all-gather: a rank's groups lie side by side), and everybody adds the groups in the same order: the
     // result has the bits of the single-GPU sum (fb_irls.cuh). Needs a world size that divides LEG_GROUPS.
     Comm &cm = Comm::get();
     const bool shared = cm.active() && LEG_GROUPS % cm.world() == 0 && !std::getenv("FB_IRLS_REPLICATED");
