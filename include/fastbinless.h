@@ -175,7 +175,9 @@ FB_API int FB_NAME(run_difference)(fb_handle *h, int ref, const fb_params *p, fb
 
 /* binless_eval_cv (fast_binless.cpp:186-233): one dataset, nlam lambda2 values
  * evaluated in order with the warm-start chain of the reference; group is the
- * checkerboard hold-out group (0 = none). outs[nlam]. */
+ * checkerboard hold-out group (0 = none). outs[nlam]. Every lambda starts from the log_signal given to fb_restore: the
+ * reference re-seeds from mat$signal, the exp'd and thresholded column (fast_binless.cpp:199,222); pass that column to
+ * fb_restore to reproduce it call for call. */
 FB_API int FB_NAME(eval_cv)(fb_handle *h, const fb_params *p, int nlam, const double *lam2,
                             unsigned group, fb_cv_out *outs);
 
