@@ -114,14 +114,15 @@ def test_cuda_reproduces_golden(gpu_lib, name):
                                                       (100, 1.3, 1e-3, 30000, 0), (64, 0.0, 1e-3, 5, 0),
                                                       (200, 2.5, 1e-12, 120, 0), (200, 2.5, 1e-12, 52, 0),
                                                       (120, 2.0, 1e-3, 30000, 30), (300, 50.0, 1e-4, 30000, 0)])
-@pytest.mark.parametrize("prox", ["hybrid", "aset", "aset_fallback", "aset_2passes", "team"])
+@pytest.mark.parametrize("prox", ["hybrid", "aset", "aset_fallback", "aset_2passes", "team", "fold"])
 def test_gfl_solve_matches_oracle(gpu_lib, oracle, monkeypatch, n, lam, conv, maxsteps, md, prox):
     """The stand-alone fused-lasso solve: same `step`, alpha trajectory, beta / z / u in the reference's slot order.
     Every variant of the chain prox: the default (taut-string team kernel for the first steps of a cold start, parallel
     active set afterwards), the parallel active set from the first step, its sequential fallback forced for every
     batch (FB_ASET_MAXPASS=0) or after two passes, and the team kernel alone (FB_PROX_ASET=0)."""
     for k, v in {"hybrid": {}, "aset": {"FB_ASET_FROM": "1"}, "aset_fallback": {"FB_ASET_FROM": "1", "FB_ASET_MAXPASS": "0"},
-                 "aset_2passes": {"FB_ASET_FROM": "1", "FB_ASET_MAXPASS": "2"}, "team": {"FB_PROX_ASET": "0"}}[prox].items():
+                 "aset_2passes": {"FB_ASET_FROM": "1", "FB_ASET_MAXPASS": "2"}, "team": {"FB_PROX_ASET": "0"},
+                 "fold": {"FB_CTL_FOLD": "1"}}[prox].items():   # the last CTA of the chain prox ends the iteration (fb_ctl.cuh)
         monkeypatch.setenv(k, v)
     rng = np.random.default_rng(n + maxsteps)
     nc = n * (n + 1) // 2
