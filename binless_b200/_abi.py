@@ -118,7 +118,7 @@ ENTRY_POINTS = ["create", "destroy", "last_error", "run_signal", "restore", "run
                 "comm_unique_id", "comm_init", "comm_destroy", "comm_rank", "comm_world", "shard_plan",
                 "create_binned", "get_mat", "mat_rows", "cv_score", "csv_write",
                 "wgfl_signal_bic", "wgfl_diff_bic", "create_multi", "handle_ngpus", "gfl_solve_multi",
-                "band_export", "gfl_last_solve_ms"]
+                "band_export", "gfl_last_solve_ms", "far_median_noalloc"]
 
 
 def _dp(a):
@@ -207,6 +207,9 @@ class FastBinlessLib:
         self._band_export = f("band_export")
         self._band_export.argtypes = [C.c_void_p, C.POINTER(fb_band_params), C.POINTER(fb_band_out)]; self._band_export.restype = C.c_int
         self._gfl_last_solve_ms = f("gfl_last_solve_ms"); self._gfl_last_solve_ms.argtypes = []; self._gfl_last_solve_ms.restype = C.c_double
+        self._far_median_noalloc = f("far_median_noalloc")
+        self._far_median_noalloc.argtypes = [C.c_int, C.c_void_p, C.c_double, C.c_int, C.c_void_p, C.c_void_p]
+        self._far_median_noalloc.restype = C.c_int
         self._kernel_launches = f("kernel_launches")
         self._kernel_launches.argtypes = [C.c_void_p]; self._kernel_launches.restype = C.c_int64
         self._gfl_solve = f("gfl_solve")
@@ -223,6 +226,13 @@ class FastBinlessLib:
         self._comm_destroy = f("comm_destroy"); self._comm_destroy.argtypes = []; self._comm_destroy.restype = C.c_int
         self._shard_plan = f("shard_plan")
         self._shard_plan.argtypes = [C.c_int, C.c_uint, C.c_int, c_ip, c_ip]; self._shard_plan.restype = C.c_int
+
+    def far_median_noalloc(self, nbins, log_signal_ptr, lam1, far_from_diag, median_ptr, stream=None):
+        """fb_far_median_noalloc: the far-cell median of band_export on caller-owned DEVICE buffers (raw addresses, e.g.
+        ``tensor.data_ptr()``); enqueues on ``stream`` (a raw cudaStream_t, None = default stream) and allocates nothing.
+        With the oracle library the two addresses are host pointers."""
+        self._check(self._far_median_noalloc(int(nbins), C.c_void_p(int(log_signal_ptr)), float(lam1), int(far_from_diag),
+                                             C.c_void_p(int(median_ptr)), C.c_void_p(int(stream or 0))), None)
 
     def csv_write(self, path, header, cols, gzip=True):
         """The reference's csvfile for caller-owned columns (fb_csv_write): gzip as built, or plain text."""

@@ -312,6 +312,26 @@ typedef struct {
 } fb_band_out;
 FB_API int FB_NAME(band_export)(fb_handle *h, const fb_band_params *p, fb_band_out *out);
 
+/* The far-cell median of fb_band_export (lam1_sig above) without any allocation. This entry point has no counterpart in
+ * the reference; it was added for callers that cannot call cudaMalloc (code
+ * under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ *   *median_dev = median over the cells with bin2 - bin1 >= far_from_diag of log(exp(soft_threshold(log_signal, lam1))),
+ * NaN when there is no such cell (R's NA). log_signal_dev (one dataset: the packed row-major triangle of
+ * nbins(nbins+1)/2 doubles, the log_signal column of fb_signal_out / fb_restore) and median_dev (one double) are DEVICE
+ * pointers owned by the caller, on the current device; `stream` is a cudaStream_t (NULL: the default stream). The call
+ * only enqueues kernels on that stream and returns: no cudaMalloc, cudaFree, copy or synchronisation; the median is in
+ * *median_dev when the stream gets there. With a bin_data() layout far_from_diag is the first diagonal whose distance
+ * exceeds far.cutoff, and the result equals lam1_sig of fb_band_export bit for bit.
+ * Scratch (the 65536-bin digit histogram of the radix select and its state) is a static device array of
+ * FB_NOALLOC_SCRATCH_BYTES that every GPU which loads the library holds until the process exits. Limit: nbins <=
+ * FB_NOALLOC_MAX_NBINS (32-bit histogram counters, grid height), beyond it FB_ERR_ARG. All calls on a device share the
+ * array: calls whose kernels can overlap on one GPU (different streams, several host threads) race and must be
+ * serialised by the caller. */
+#define FB_NOALLOC_MAX_NBINS 65535
+#define FB_NOALLOC_SCRATCH_BYTES (65536 * 4 + 256)
+FB_API int FB_NAME(far_median_noalloc)(int nbins, const double *log_signal_dev, double lam1, int far_from_diag,
+                                       double *median_dev, void *stream);
+
 /* Diagnostic: device time (CUDA events on the solver's stream, milliseconds) of the ADMM loop of the last fb_gfl_solve /
  * fb_gfl_solve_multi call made by this host thread: uploads, set-up and state export are outside it. */
 FB_API double FB_NAME(gfl_last_solve_ms)(void);

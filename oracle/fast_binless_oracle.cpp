@@ -1480,6 +1480,26 @@ FB_API int fbo_comm_init(int rank, int world, const void *) {
 }
 FB_API int fbo_comm_destroy(void) { return FB_OK; }
 FB_API double fbo_gfl_last_solve_ms(void) { return 0.0; }
+/* fb_far_median_noalloc has no counterpart in the reference (fastbinless.h); the oracle side of the ABI is the same
+ * median on HOST pointers, so that tests can check the device result: R's median of log(exp(soft(log_signal, lam1))) over
+ * the cells with bin2 - bin1 >= far_from_diag (chromosome.R:270-276), NaN for none. */
+FB_API int fbo_far_median_noalloc(int nbins, const double *log_signal, double lam1, int far_from_diag, double *median, void *) {
+    if (!log_signal || !median || nbins < 1 || far_from_diag < 0) { g_create_error = "invalid argument"; return FB_ERR_ARG; }
+    std::vector<double> v;
+    int64_t pos = 0;
+    for (int i = 0; i < nbins; ++i)
+        for (int j = i; j < nbins; ++j, ++pos)
+            if (j - i >= far_from_diag) {
+                const double x = log_signal[pos];
+                const double s = x > 0 ? std::max(0., x - lam1) : std::min(0., x + lam1);
+                v.push_back(std::log(std::exp(s)));
+            }
+    if (v.empty()) { *median = NAN; return FB_OK; }
+    std::sort(v.begin(), v.end());
+    const size_t n = v.size();
+    *median = (n & 1) ? v[(n - 1) / 2] : (v[(n - 1) / 2] + v[n / 2]) / 2;
+    return FB_OK;
+}
 /* single-process multi-GPU entry points: the reference is one thread on one CPU, so "ngpus" changes nothing here */
 FB_API int fbo_create(int nbins, const fb_mat *mat, fb_handle **out);
 FB_API int fbo_create_multi(int nbins, const fb_mat *mat, int, fb_handle **out) { return fbo_create(nbins, mat, out); }
