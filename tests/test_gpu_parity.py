@@ -152,6 +152,29 @@ def test_gfl_long_chain_mode_matches_oracle(gpu_lib, oracle, monkeypatch, n, lam
         assert np.array_equal(ref[k], b[k]), k       # 1/m is the same correctly rounded value either way
 
 
+@pytest.mark.parametrize("n,lam,steps,check_oracle", [(1500, 2.5, 14, True), (1300, 400.0, 14, False), (700, 2.5, 30, False)])
+def test_gfl_scratch_window_mode_matches_shared_memory_mode(gpu_lib, oracle, monkeypatch, n, lam, steps, check_oracle):
+    """Chains whose prefix sums live in global scratch (above ~4500 bins) are searched through a sliding shared-memory
+    window per warp (fb_taut.cuh, WLEN = 512 cells). Forced at sizes with chains longer than the window, short and very
+    long segments (lam = 400: segments far longer than the window): bit-identical to the shared-memory mode."""
+    rng = np.random.default_rng(n)
+    nc = n * (n + 1) // 2
+    y = np.repeat(rng.normal(0, 1, nc // 40 + 1), 40)[:nc] + rng.normal(0, 0.5, nc)
+    w = rng.uniform(0, 3, size=nc); w[rng.random(nc) < 0.1] = 0
+    monkeypatch.setenv("FB_PROX_ASET", "0")
+    ref = gfl_solve(gpu_lib, n, y, w, lam, 1e-12, steps, 0)
+    monkeypatch.setenv("FB_PROX_GS", "1")
+    b = gfl_solve(gpu_lib, n, y, w, lam, 1e-12, steps, 0)
+    assert ref["steps"] == b["steps"] and ref["alpha"] == b["alpha"]
+    for k in ("beta", "z", "u", "beta_full"):
+        assert np.array_equal(ref[k], b[k]), k
+    if check_oracle:
+        a = gfl_solve(oracle, n, y, w, lam, 1e-12, steps, 0)
+        assert a["steps"] == b["steps"] and a["alpha"] == b["alpha"]
+        for k in ("beta", "z", "u", "beta_full"):
+            assert maxabs(a[k], b[k]) < ATOL, k
+
+
 def test_gfl_warm_start_chain(gpu_lib, oracle):
     n = 120; nc = n * (n + 1) // 2
     rng = np.random.default_rng(3)
