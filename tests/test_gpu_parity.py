@@ -153,10 +153,9 @@ def test_gfl_long_chain_mode_matches_oracle(gpu_lib, oracle, monkeypatch, n, lam
 
 
 @pytest.mark.parametrize("n,lam,steps,check_oracle", [(1500, 2.5, 14, True), (1300, 400.0, 14, False), (700, 2.5, 30, False)])
-def test_gfl_scratch_window_mode_matches_shared_memory_mode(gpu_lib, oracle, monkeypatch, n, lam, steps, check_oracle):
-    """Chains whose prefix sums live in global scratch (above ~4500 bins) are searched through a sliding shared-memory
-    window per warp (fb_taut.cuh, WLEN = 512 cells). Forced at sizes with chains longer than the window, short and very
-    long segments (lam = 400: segments far longer than the window): bit-identical to the shared-memory mode."""
+def test_gfl_scratch_mode_matches_shared_memory_mode(gpu_lib, oracle, monkeypatch, n, lam, steps, check_oracle):
+    """The team kernel with the chains' prefix sums in global scratch (what runs above ~4500 bins), forced at sizes the
+    oracle still finishes, with short and with very long segments (lam = 400): bit-identical to the shared-memory mode."""
     rng = np.random.default_rng(n)
     nc = n * (n + 1) // 2
     y = np.repeat(rng.normal(0, 1, nc // 40 + 1), 40)[:nc] + rng.normal(0, 0.5, nc)
