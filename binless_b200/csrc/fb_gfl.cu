@@ -587,6 +587,17 @@ k_ctl(GflCtl *ctl, const double *__restrict__ partials, int npart, int64_t ncell
 }
 
 // applies a pending dual rescale after the last iteration of a solve
+// The control block to the host by stores from an SM into mapped pinned memory: a cudaMemcpy of these few bytes would
+// queue in the device-to-host copy engine behind any bulk download another stream has in flight (the early output
+// columns of Model::run_signal: 4 solves x up to 6 ms of waiting).
+__global__ void k_export_ctl(const GflCtl *__restrict__ ctl, GflCtl *__restrict__ host_ctl) {
+    static_assert(sizeof(GflCtl) % 4 == 0, "word copy");
+    const unsigned *src = reinterpret_cast<const unsigned *>(ctl);
+    volatile unsigned *dst = reinterpret_cast<volatile unsigned *>(host_ctl);
+    for (unsigned k = threadIdx.x; k < sizeof(GflCtl) / 4; k += blockDim.x) dst[k] = src[k];
+    __threadfence_system();
+}
+
 __global__ void k_rescale_u(double *__restrict__ u, int64_t n, int mode, double inflate) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) u[i] = (mode == 1) ? u[i] / inflate : u[i] * inflate;
@@ -1110,7 +1121,7 @@ int GflSolver::optimize(const double *d_y_tri, const double *d_w_tri, double lam
     if (!done && use_graph_) {
         if (!graph_exec_) build_graph();
         FB_CUDA(cudaGraphLaunch(graph_exec_, st_));
-        FB_CUDA(cudaMemcpyAsync(h_ctl_, ctl_.p, sizeof(GflCtl), cudaMemcpyDeviceToHost, st_));
+        k_export_ctl<<<1, 32, 0, st_>>>(ctl_.p, h_ctl_);
         FB_CUDA(cudaStreamSynchronize(st_));
         if (!h_ctl_->done) throw CudaError("the captured ADMM loop ended without setting done");
         kernel_launches += ((use_aset_ ? 4 : 3) - (fold_ctl_ ? 1 : 0)) * (int64_t)(h_ctl_->step - 1);
@@ -1123,7 +1134,7 @@ int GflSolver::optimize(const double *d_y_tri, const double *d_w_tri, double lam
         if (const char *e = std::getenv("FB_SHARD_POLL")) batch = std::max(1, std::atoi(e));   // development aid
         for (int b = 0; b < batch; ++b) { iteration(y, w, parity); parity ^= 1; }
         FB_LAUNCH_CHECK();
-        FB_CUDA(cudaMemcpyAsync(h_ctl_, ctl_.p, sizeof(GflCtl), cudaMemcpyDeviceToHost, st_));
+        k_export_ctl<<<1, 32, 0, st_>>>(ctl_.p, h_ctl_);
         FB_CUDA(cudaStreamSynchronize(st_));
         if (!h_ctl_->done) tflush();
         done = h_ctl_->done != 0;

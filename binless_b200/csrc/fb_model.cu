@@ -89,6 +89,13 @@ void write_signal_csv(const char *path, int64_t N, const double *const cols[7]) 
                  !(e && std::atoi(e) != 0));
 }
 
+// true for host memory the driver can DMA into directly (cudaHostAlloc / cudaHostRegister / managed)
+bool host_pinned(const void *p) {
+    cudaPointerAttributes at{};
+    if (cudaPointerGetAttributes(&at, p) != cudaSuccess) { cudaGetLastError(); return false; }
+    return at.type == cudaMemoryTypeHost || at.type == cudaMemoryTypeManaged;
+}
+
 // copies of at least this many bytes to / from pageable host memory are pipelined through pinned staging
 // (FB_STAGE_MIN_MB lowers the limit so that the tests exercise the path at small sizes)
 size_t stage_min_bytes() {
@@ -125,14 +132,21 @@ void Model::open_stream() {
     FB_CUDA(cudaStreamCreateWithFlags(&st_, cudaStreamNonBlocking));
     FB_CUDA(cudaEventCreate(&ev0_));
     FB_CUDA(cudaEventCreate(&ev1_));
+    FB_CUDA(cudaStreamCreateWithFlags(&st_dl_, cudaStreamNonBlocking));
+    FB_CUDA(cudaEventCreateWithFlags(&ev_in_, cudaEventDisableTiming));
+    FB_CUDA(cudaEventCreateWithFlags(&ev_sk_, cudaEventDisableTiming));
+    FB_CUDA(cudaEventCreateWithFlags(&ev_dl_, cudaEventDisableTiming));
 }
 void Model::close_stream() {
     flo_.reset();
     if (st_) cudaStreamSynchronize(st_); // buffers go back to the block cache only when nothing uses them any more
+    if (st_dl_) cudaStreamSynchronize(st_dl_);
     if (ev0_) cudaEventDestroy(ev0_);
     if (ev1_) cudaEventDestroy(ev1_);
+    for (cudaEvent_t e : {ev_in_, ev_sk_, ev_dl_}) if (e) cudaEventDestroy(e);
     if (st_) cudaStreamDestroy(st_);
-    st_ = nullptr; ev0_ = ev1_ = nullptr;
+    if (st_dl_) cudaStreamDestroy(st_dl_);
+    st_ = st_dl_ = nullptr; ev0_ = ev1_ = ev_in_ = ev_sk_ = ev_dl_ = nullptr;
 }
 
 // a constructor that throws (rejected input: the normal validation path) does not run the destructor
@@ -664,6 +678,35 @@ void Model::run_signal(const fb_params *p, fb_signal_out *out) {
     int64_t n_solves = 0, iters = 0, cell_iters = 0;
     bool sig_partial = false;
     out->nsteps = 0; out->converged = 0;
+    // get_as_dataframe columns (fast_dataframe.cpp:9-110). Four of them are final BEFORE the fused-lasso solves of the step
+    // that turns out to be the last one: phihat and weight (made by signal_yw for the solves) and biasmat / decaymat (the
+    // bias and decay legs are not touched after it; fit_expo changes the exposures only). A signal step that CAN end the
+    // loop (the tolerance test below needs current_tol_val <= 1.01 tol_val before the step, or it is step nouter) sends
+    // them to the caller's buffers on a second stream while the solves run (PCIe is idle then); the copies of the step
+    // that ends the loop stand, those of an earlier step are overwritten (by a later early copy on the same stream, or by
+    // the downloads at the end, which wait for that stream). A step that finds the previous early copy still in flight
+    // does not add another. Only for pinned host buffers: a copy to pageable memory would hold this thread.
+    // FB_NO_EARLY_DOWNLOAD=1 keeps everything for the end.
+    DevBuf<double> lam1_d(D), cols;
+    DevBuf<int32_t> pl_labels, pl_parent, pl_scan;     // patch numbers made on the second stream (below)
+    lam1_d.upload(lam1.data(), D, st_);
+    const bool csv = p->csv_out && p->csv_out[0];
+    double *want[5] = {out->background, out->biasmat, out->decaymat, out->signal, out->binless};
+    double *dcol[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+    {
+        int nwant = 0;
+        for (double *w : want) nwant += (w != nullptr || csv);
+        if (nwant) {
+            cols.alloc((size_t)nwant * N);
+            int k = 0;
+            for (int c = 0; c < 5; ++c) if (want[c] || csv) dcol[c] = cols.p + (size_t)(k++) * N;
+        }
+    }
+    double *early_h[4] = {out->phihat, out->weight, out->biasmat, out->decaymat};
+    bool early = !std::getenv("FB_NO_EARLY_DOWNLOAD") && (early_h[0] || early_h[1] || early_h[2] || early_h[3]);
+    for (double *h : early_h) if (h && !host_pinned(h)) early = false;
+    unsigned early_step = 0;                 // the signal step whose early copies are in the caller's buffers (0: none)
+    struct DlGuard { cudaStream_t s; ~DlGuard() { if (s) cudaStreamSynchronize(s); } } dl_guard{early ? st_dl_ : nullptr};
     for (unsigned step = 1; step <= p->nouter; ++step) {
         check_interrupt();
         if (p->verbose) std::printf("step %u", step);
@@ -683,6 +726,21 @@ void Model::run_signal(const fb_params *p, fb_signal_out *out) {
             if (partial) FB_CUDA(cudaMemcpyAsync(tab_sig_.p, tab_.p, tab_.n * sizeof(double), cudaMemcpyDeviceToDevice, st_));
             sig_partial = partial;
             kernel_launches += 1;
+            if (early && (current_tol_val <= tol_val * 1.01 || step == p->nouter) && cudaEventQuery(ev_dl_) == cudaSuccess) {
+                FB_CUDA(cudaEventRecord(ev_in_, st_));
+                FB_CUDA(cudaStreamWaitEvent(st_dl_, ev_in_, 0));
+                if (dcol[1] || dcol[2]) {
+                    output_signal(t_, tables(tab_), nobs_.p, phi_.p, lam1_d.p, nullptr, dcol[1], dcol[2], nullptr, nullptr, st_dl_);
+                    kernel_launches += 1;
+                }
+                FB_CUDA(cudaEventRecord(ev_sk_, st_dl_));
+                const double *src[4] = {partial ? nullptr : phihat_.p, partial ? nullptr : wgt_.p, dcol[1], dcol[2]};
+                for (int c = 0; c < 4; ++c)
+                    if (early_h[c] && src[c])
+                        FB_CUDA(cudaMemcpyAsync(early_h[c], src[c], (size_t)N * sizeof(double), cudaMemcpyDeviceToHost, st_dl_));
+                FB_CUDA(cudaEventRecord(ev_dl_, st_dl_));
+                early_step = step;
+            }
             for (int d = 0; d < D; ++d) {
                 g_pt.start();
                 const int steps = flo.optimize(phihat_.p + (size_t)d * nc, wgt_.p + (size_t)d * nc, lam2[d], flo_tol);
@@ -702,6 +760,7 @@ void Model::run_signal(const fb_params *p, fb_signal_out *out) {
             precision(t_, tables(tab_), tables(tab_), phi_.p, phi_new_.p, scratch_.p, scratch_.p + 8, st_, share());
             kernel_launches += 3;
             std::swap(phi_.p, phi_new_.p);
+            if (early_step == step) FB_CUDA(cudaStreamWaitEvent(st_, ev_sk_, 0));   // fit_expo re-uploads the tables the early kernel read
         }
         FB_CUDA(cudaMemcpyAsync(prec_h_.p, scratch_.p + 8, 3 * sizeof(double), cudaMemcpyDeviceToHost, st_));
         FB_CUDA(cudaStreamSynchronize(st_));
@@ -733,25 +792,43 @@ void Model::run_signal(const fb_params *p, fb_signal_out *out) {
 
     // get_as_dataframe, Signal overload (fast_dataframe.cpp:9-110)
     {
-        DevBuf<double> lam1_d(D), cols;
-        lam1_d.upload(lam1.data(), D, st_);
-        const bool csv = p->csv_out && p->csv_out[0];
-        double *want[5] = {out->background, out->biasmat, out->decaymat, out->signal, out->binless};
-        int nwant = 0;
-        for (double *w : want) nwant += (w != nullptr || csv);
-        double *dcol[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
-        if (nwant) {
-            cols.alloc((size_t)nwant * N);
-            int k = 0;
-            for (int c = 0; c < 5; ++c) if (want[c] || csv) dcol[c] = cols.p + (size_t)(k++) * N;
+        // the early copies stand when the loop ended on the signal step that made them
+        const bool have_early = early_step != 0 && early_step == (unsigned)out->nsteps;
+        const auto tail0 = std::chrono::steady_clock::now();
+        const bool early_landed = early_step != 0 && cudaEventQuery(ev_dl_) == cudaSuccess;
+        const bool have_yw = have_early && !sig_partial;
+        if (early_step) FB_CUDA(cudaStreamWaitEvent(st_, ev_dl_, 0));     // biasmat / decaymat are written again below
+        // the patch numbers (six kernels per dataset) on the second stream, under the column downloads of this one
+        if (early && out->patchno && host_pinned(out->patchno)) {
+            FB_CUDA(cudaEventRecord(ev_in_, st_));
+            FB_CUDA(cudaStreamWaitEvent(st_dl_, ev_in_, 0));
+            pl_labels.alloc(N);
+            if (!p->compute_patchnos) { fill_i32(pl_labels.p, N, -1, st_dl_); kernel_launches += 1; }
+            else {
+                pl_parent.alloc(nc); pl_scan.alloc(nc + nc / 4096 + 8);
+                for (int d = 0; d < D; ++d) {
+                    patch_labels(n, tol_val, phi_.p + (size_t)d * nc, pl_parent.p, pl_scan.p, pl_labels.p + (size_t)d * nc, st_dl_);
+                    kernel_launches += 6;
+                }
+            }
+            FB_CUDA(cudaMemcpyAsync(out->patchno, pl_labels.p, (size_t)N * sizeof(int32_t), cudaMemcpyDeviceToHost, st_dl_));
+        }
+        if (cols.p) {
             output_signal(t_, tables(tab_), nobs_.p, phi_.p, lam1_d.p, dcol[0], dcol[1], dcol[2], dcol[3], dcol[4], st_);
             kernel_launches += 1;
-            for (int c = 0; c < 5; ++c) download(want[c], dcol[c], N);
+            for (int c = 0; c < 5; ++c)
+                if (!(have_early && (c == 1 || c == 2))) download(want[c], dcol[c], N);
         }
-        download(out->phihat, phihat_.p, N);
-        download(out->weight, wgt_.p, N);
+        if (!have_yw) {
+            download(out->phihat, phihat_.p, N);
+            download(out->weight, wgt_.p, N);
+        }
         download(out->log_signal, phi_.p, N);
         FB_CUDA(cudaStreamSynchronize(st_));
+        if (g_pt.on)
+            std::fprintf(stderr, "[fb timing] columns to the host after the loop %.2f ms (early copies of step %u: %s, %s)\n",
+                         std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tail0).count(), early_step,
+                         have_early ? "kept" : "not used", !early_step ? "none made" : early_landed ? "landed before the loop ended" : "still in flight");
         if (csv) { // fast_dataframe.cpp:23-57: phihat, weight, biasmat, decaymat, signal, binless, background
             std::vector<double> hbuf((size_t)7 * N);
             const double *src[7] = {phihat_.p, wgt_.p, dcol[1], dcol[2], dcol[3], dcol[4], dcol[0]};
@@ -764,7 +841,14 @@ void Model::run_signal(const fb_params *p, fb_signal_out *out) {
             write_signal_csv(p->csv_out, N, hc);
         }
     }
-    patchnos(phi_.p, tol_val, p->compute_patchnos != 0, out->patchno);
+    {
+        const auto tp0 = std::chrono::steady_clock::now();
+        if (pl_labels.p) FB_CUDA(cudaStreamSynchronize(st_dl_));
+        else patchnos(phi_.p, tol_val, p->compute_patchnos != 0, out->patchno);
+        if (g_pt.on)
+            std::fprintf(stderr, "[fb timing] patch numbers (kernels + download) %.2f ms\n",
+                         std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tp0).count());
+    }
     // leg states (fast_binless.cpp:179-183)
     if (out->biases.estimate) std::memcpy(out->biases.estimate, bias_est_.data(), bias_est_.size() * sizeof(double));
     out->biases.n = nb_bias_; out->biases.mean = 0;

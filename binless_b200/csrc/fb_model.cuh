@@ -58,6 +58,9 @@ private:
     Tri t_;
     cudaStream_t st_ = nullptr;
     cudaEvent_t ev0_ = nullptr, ev1_ = nullptr;
+    // early download of the output columns that are final before the last fused-lasso solves (run_signal): a second stream
+    cudaStream_t st_dl_ = nullptr;
+    cudaEvent_t ev_in_ = nullptr, ev_sk_ = nullptr, ev_dl_ = nullptr;
     // device-resident matrix
     DevBuf<int32_t> obs_, nobs_;
     DevBuf<double> phi_, phi_new_, phihat_, wgt_;

@@ -390,6 +390,38 @@ def test_band_export_matches_oracle(gpu_lib, oracle, n, D, far, maxdiag):
     assert eg["band_bin1"].size == sum(min(maxdiag + 1, n - i) for i in range(n))
 
 
+@pytest.mark.parametrize("n,D,seed,kw", [(200, 2, 1, {}), (129, 1, 12, {}), (96, 3, 7, {"nouter": 2}), (150, 2, 5, {"tol_val": 0.02}),
+                                          (64, 2, 9, {"compute_patchnos": False})])
+def test_early_download_into_pinned_buffers_is_identical(gpu_lib, monkeypatch, n, D, seed, kw):
+    """With pinned output buffers fb_run_signal sends phihat / weight / biasmat / decaymat to the host on a second stream
+    while the last fused-lasso solves run. Every column equals, bit for bit, the call with pageable buffers (no early
+    copies) and the call with the early copies switched off; also when the loop stops at nouter or takes many steps."""
+    import torch
+    mat = synth(n, D, 5000, seed)
+    N = D * n * (n + 1) // 2
+    names = ("background", "biasmat", "decaymat", "signal", "binless", "phihat", "weight", "log_signal")
+
+    def pinned():
+        t = {k: torch.full((N,), float("nan"), dtype=torch.float64).pin_memory() for k in names}
+        t["patchno"] = torch.zeros(N, dtype=torch.int32).pin_memory()
+        return t, {k: v.numpy() for k, v in t.items()}
+
+    with gpu_lib.create(mat, n) as h:
+        plain = h.run_signal(0.49, 2.5, 0.1, **kw)
+        keep1, b1 = pinned()
+        early = h.run_signal(0.49, 2.5, 0.1, buffers=b1, **kw)
+        again = h.run_signal(0.49, 2.5, 0.1, buffers=b1, **kw)          # on buffers that hold the previous results
+        monkeypatch.setenv("FB_NO_EARLY_DOWNLOAD", "1")
+        keep2, b2 = pinned()
+        late = h.run_signal(0.49, 2.5, 0.1, buffers=b2, **kw)
+    assert plain["diagnostics"]["nsteps"] == early["diagnostics"]["nsteps"] == late["diagnostics"]["nsteps"]
+    for k in names + ("patchno",):
+        assert np.array_equal(plain[k], early[k]), k
+        assert np.array_equal(plain[k], again[k]), k
+        assert np.array_equal(plain[k], late[k]), k
+    del keep1, keep2
+
+
 def _jittered(n, D, seed):
     """a matrix that is NOT a bin_data() layout: distance varies inside a diagonal, positions differ between datasets"""
     mat = synth(n, D, 5000, seed)
