@@ -228,6 +228,7 @@ FB_API int fb_set_interrupt_cb(fb_handle *h, int (*cb)(void *), void *arg) {
 
 FB_API void fb_release_cached_memory(void) {
     cudaDeviceSynchronize();
+    fb::release_idle_solvers();
     fb::BlockCache::device().trim();
     fb::BlockCache::host().trim();
 }

@@ -89,6 +89,9 @@ public:
     GflSolver(int nbins, unsigned maxdiag, cudaStream_t stream);
     ~GflSolver();
     void reset();                      // cold start (GFLLibraryTriangleImpl::reset)
+    // an idle solver continues on another stream (the captured ADMM graph does not depend on the stream it was built on)
+    void rebind(cudaStream_t stream) { st_ = stream; }
+    bool sharded() const { return sharded_; }
     // runs ADMM to convergence; returns `step` like graph_fused_lasso_weight_warm
     int optimize(const double *d_y_tri, const double *d_w_tri, double lam2, double converge);
     // clamp(+-50) of the solution scattered to the full packed triangle

@@ -138,7 +138,7 @@ void Model::open_stream() {
     FB_CUDA(cudaEventCreateWithFlags(&ev_dl_, cudaEventDisableTiming));
 }
 void Model::close_stream() {
-    flo_.reset();
+    retire_solver();
     if (st_) cudaStreamSynchronize(st_); // buffers go back to the block cache only when nothing uses them any more
     if (st_dl_) cudaStreamSynchronize(st_dl_);
     if (ev0_) cudaEventDestroy(ev0_);
@@ -226,6 +226,8 @@ void Model::ingest(int nbins, const fb_mat *m) {
     t_.n = nbins; t_.D = (int)D; t_.ncells = ncells;
 
     // start the uploads, validate on the host meanwhile
+    const auto ti0 = std::chrono::steady_clock::now();
+    auto since = [&] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - ti0).count(); };
     obs_.alloc(N); nobs_.alloc(N);
     auto checks = std::async(std::launch::async, [&]() -> const char * {
         if (m->bin1 || m->bin2 || m->name) {
@@ -269,8 +271,11 @@ void Model::ingest(int nbins, const fb_mat *m) {
         scratch_.alloc(4096);
         keys_.alloc((size_t)(2 * n + 1) * D + 8);
     }
+    const double t_enq = since();
     const char *e = checks.get();
+    const double t_chk = since();
     FB_CUDA(cudaStreamSynchronize(st_));
+    if (g_pt.on) std::fprintf(stderr, "[fb timing] ingest: uploads enqueued %.2f ms, host validation done %.2f ms, uploads done %.2f ms\n", t_enq, t_chk, since());
     if (e == kLayoutMsg || std::getenv("FB_FORCE_CELL_BINS")) {
         // not a bin_data() layout (or the test aid asks for it): bin every cell like the reference does (util.cpp:56-111)
         if (e && e != kLayoutMsg) throw ArgError(e);
@@ -525,13 +530,84 @@ void Model::fit_decay(int mode) {
     upload_tables();
 }
 
+// Idle single-GPU solver objects of destroyed handles, kept for the next handle of the same shape on the same device:
+// fast_binless is called once per locus on same-shaped matrices, and building the object (chain batches of the active
+// set, tables, the captured ADMM graph) costs 1.7 ms at 2400 bins against 25 ms for the whole call. The key holds the
+// values of the environment switches the constructor reads, so test variants never meet each other's objects.
+// fb_release_cached_memory() empties the pool. Never destroyed at exit (the CUDA context may be gone by then).
+namespace {
+struct SolverPool {
+    struct Item { int dev, n; unsigned maxdiag; std::string env; std::unique_ptr<GflSolver> s; };
+    std::mutex mu;
+    std::vector<Item> items;
+    static constexpr size_t kMax = 2;
+    static std::string env_sig() {
+        static const char *names[] = {"FB_ASET_FROM", "FB_CTL_FOLD", "FB_NO_GRAPH", "FB_PROX_ASET", "FB_PROX_GS", "FB_PROX_RTAB",
+                                      "FB_PROX_TRACE", "FB_ASET_CAP", "FB_ASET_MAXPASS", "FB_ASET_STATS", "FB_SHARD_TIMING"};
+        std::string sig;
+        for (const char *nm : names) { const char *v = std::getenv(nm); sig += v ? v : "~"; sig += '|'; }
+        return sig;
+    }
+    std::unique_ptr<GflSolver> take(int dev, int n, unsigned maxdiag) {
+        const std::string sig = env_sig();
+        std::lock_guard<std::mutex> lock(mu);
+        for (size_t k = 0; k < items.size(); ++k)
+            if (items[k].dev == dev && items[k].n == n && items[k].maxdiag == maxdiag && items[k].env == sig) {
+                std::unique_ptr<GflSolver> s = std::move(items[k].s);
+                items.erase(items.begin() + (long)k);
+                return s;
+            }
+        return nullptr;
+    }
+    void give(int dev, int n, unsigned maxdiag, std::unique_ptr<GflSolver> s) {
+        std::unique_ptr<GflSolver> drop;        // destroyed outside the lock
+        {
+            std::lock_guard<std::mutex> lock(mu);
+            if (items.size() >= kMax) { drop = std::move(items.front().s); items.erase(items.begin()); }
+            items.push_back(Item{dev, n, maxdiag, env_sig(), std::move(s)});
+        }
+    }
+    void clear() {
+        std::vector<Item> all;
+        { std::lock_guard<std::mutex> lock(mu); all.swap(items); }
+        for (auto &it : all) {       // a solver frees its buffers into the cache of ITS device
+            int cur = 0; cudaGetDevice(&cur);
+            cudaSetDevice(it.dev); it.s.reset(); cudaSetDevice(cur);
+        }
+    }
+};
+SolverPool &solver_pool() {
+    static SolverPool *p = [] { BlockCache::pressure_hook().store(&release_idle_solvers); return new SolverPool(); }();
+    return *p;
+}
+} // namespace
+
+void release_idle_solvers() { solver_pool().clear(); }
+
 // The fused-lasso object of a call: a FRESH FusedLassoGaussianEstimator<GFLLibrary> in the reference (fast_binless.cpp:122).
 // Its structure (chain batches, the captured ADMM graph, the device arrays) depends on (nbins, maxdiag) only, so the handle
 // keeps one and hands it out reset to the cold state (beta = z = u = 0, alpha = 5, counters 0).
+// the handle's solver goes to the pool (idle, its stream drained) or, when it is shared between GPUs, away
+void Model::retire_solver() {
+    if (!flo_) return;
+    if (!flo_->sharded() && st_) {
+        int dev = 0;
+        if (cudaStreamSynchronize(st_) == cudaSuccess && cudaGetDevice(&dev) == cudaSuccess) {
+            flo_->rebind(nullptr);
+            solver_pool().give(dev, t_.n, flo_maxdiag_, std::move(flo_));
+        }
+    }
+    flo_.reset();
+}
+
 GflSolver &Model::solver(unsigned maxdiag) {
     if (!flo_ || flo_maxdiag_ != maxdiag || flo_comm_ != (Comm::get().active() ? Comm::get().world() : 1)) {
-        flo_.reset();
-        flo_.reset(new GflSolver(t_.n, maxdiag, st_));
+        retire_solver();
+        int dev = 0;
+        FB_CUDA(cudaGetDevice(&dev));
+        if (!Comm::get().active()) flo_ = solver_pool().take(dev, t_.n, maxdiag);
+        if (flo_) { flo_->rebind(st_); flo_->reset(); }
+        else flo_.reset(new GflSolver(t_.n, maxdiag, st_));
         flo_maxdiag_ = maxdiag; flo_comm_ = Comm::get().active() ? Comm::get().world() : 1;
     } else flo_->reset();
     flo_->kernel_launches = 0;
@@ -671,7 +747,11 @@ void Model::run_signal(const fb_params *p, fb_signal_out *out) {
     fit_bias(MODE_POISSON);
 
     double current_tol_val = 1.;
+    const auto tsolver0 = std::chrono::steady_clock::now();
     GflSolver &flo = solver(p->maxdiag); // shared by all datasets: the flos copies share one strategy (GFLLibrary.hpp:59)
+    if (g_pt.on)
+        std::fprintf(stderr, "[fb timing] fused-lasso solver object (plans, tables) %.2f ms\n",
+                     std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tsolver0).count());
     double flo_tol = current_tol_val / 20.;
     const std::vector<double> lam2 = broadcast(p->lam2, p->n_lam2, D);
     const std::vector<double> lam1 = broadcast(p->lam1, p->n_lam1, D);

@@ -102,6 +102,7 @@ private:
     unsigned flo_maxdiag_ = 0; int flo_comm_ = 1;
     GflSolver &solver(unsigned maxdiag);
     Share share() const;
+    void retire_solver();
     void open_stream();
     void close_stream();
     void ingest_cells(const fb_mat *mat);
@@ -124,5 +125,6 @@ private:
 };
 
 extern thread_local std::string g_last_error;
+void release_idle_solvers();      // the pool of idle solver objects of destroyed handles (fb_model.cu)
 
 } // namespace fb

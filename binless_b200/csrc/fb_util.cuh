@@ -5,6 +5,7 @@
 #include <cstdio>
 #include <exception>
 #include <map>
+#include <atomic>
 #include <mutex>
 #include <stdexcept>
 #include <string>
@@ -43,8 +44,9 @@ public:
         }
         void *p = nullptr;
         cudaError_t e = pinned_ ? cudaMallocHost(&p, bytes) : cudaMalloc(&p, bytes);
-        if (e != cudaSuccess) { // give the cached blocks back and retry once
+        if (e != cudaSuccess) { // give the cached blocks (and the idle solver objects that hold some) back and retry once
             cudaGetLastError();
+            if (void (*hook)() = pressure_hook().load()) hook();
             trim();
             e = pinned_ ? cudaMallocHost(&p, bytes) : cudaMalloc(&p, bytes);
         }
@@ -75,6 +77,8 @@ public:
         return c[dev & 15];
     }
     static BlockCache &host() { static BlockCache c(true); return c; }
+    // called before the cache is emptied because an allocation failed: owners of idle objects let them go (fb_model.cu)
+    static std::atomic<void (*)()> &pressure_hook() { static std::atomic<void (*)()> h{nullptr}; return h; }
 private:
     bool pinned_;
     std::mutex mu_;
