@@ -29,6 +29,15 @@ struct PhaseTimer {
 };
 PhaseTimer g_pt;
 
+// pos1[k] == pi, pos2[k] == pj[k], distance[k] == dj[k] for every k < len
+__attribute__((optimize("O3"))) bool row_is_layout(const int32_t *__restrict__ p1, const int32_t *__restrict__ p2,
+                                                   const double *__restrict__ dd, const int32_t pi, const int32_t *__restrict__ pj,
+                                                   const double *__restrict__ dj, const int64_t len) {
+    int bad = 0;
+    for (int64_t k = 0; k < len; ++k) bad |= (p1[k] != pi) | (p2[k] != pj[k]) | (dd[k] != dj[k]);
+    return bad == 0;
+}
+
 const char *kLayoutMsg = "pos1/pos2 do not depend on the bin only or distance not on bin2-bin1 only";   // -> per-cell fallback
 const char *kSizeMsg = "Input size should be N(N+1)/2 dense matrix of observed counts for each dataset";
 
@@ -249,16 +258,14 @@ void Model::ingest(int nbins, const fb_mat *m) {
                                     : "mat must be sorted by (name, bin1, bin2) and hold every cell of the upper triangle";
         }
         pos_.resize(n); dist_.resize(n);
-        for (int64_t r = 0; r < n; ++r) { pos_[r] = m->pos1[rm_start(r, n)]; dist_[r] = m->distance[r]; }
+        std::vector<int32_t> ipos(n);
+        for (int64_t r = 0; r < n; ++r) { ipos[r] = m->pos1[rm_start(r, n)]; pos_[r] = ipos[r]; dist_[r] = m->distance[r]; }
         return par_rows(D, [&](int64_t d, int64_t i) -> const char * {
-            const int64_t base = d * ncells + rm_start(i, n);
-            const double pi = pos_[i];
-            for (int64_t j = i; j < n; ++j) {
-                const int64_t g = base + (j - i);
-                if ((double)m->pos1[g] != pi || (double)m->pos2[g] != pos_[j] || m->distance[g] != dist_[j - i])
-                    return kLayoutMsg;
-            }
-            return nullptr;
+            // a row at a time, without branches (the compiler vectorises it): pos1 is the row's position, pos2 the
+            // positions of the bins from i on, distance the per-diagonal table (NaN compares unequal: not a layout)
+            return row_is_layout(m->pos1 + d * ncells + rm_start(i, n), m->pos2 + d * ncells + rm_start(i, n),
+                                 m->distance + d * ncells + rm_start(i, n), ipos[i], ipos.data() + i, dist_.data(), n - i)
+                       ? nullptr : kLayoutMsg;
         });
     });
     upload_bytes(obs_.p, m->observed, N * sizeof(int32_t));
@@ -630,15 +637,16 @@ void Model::check_interrupt() {
 // allocated PAGEABLE vectors: there the driver's own staging runs at a few GB/s (10 GB of log_signal at 50 000 bins:
 // 2.5 s, most of it first-touch page faults on one thread), so large pageable copies are pipelined through pinned
 // staging buffers and scattered to the destination by several host threads while the next chunk is in flight.
-void Model::download_bytes(void *h_dst, const void *d_src, size_t bytes) {
+void Model::download_bytes(void *h_dst, const void *d_src, size_t bytes, cudaStream_t st) {
     if (!h_dst || !bytes) return;
+    if (!st) st = st_;
     constexpr size_t CHUNK = size_t(32) << 20;
     cudaPointerAttributes at{};
     const bool known = cudaPointerGetAttributes(&at, h_dst) == cudaSuccess;
     if (!known) cudaGetLastError();
     const bool pageable = !known || at.type == cudaMemoryTypeUnregistered;
     if (!pageable || bytes < stage_min_bytes()) {
-        FB_CUDA(cudaMemcpyAsync(h_dst, d_src, bytes, cudaMemcpyDeviceToHost, st_));
+        FB_CUDA(cudaMemcpyAsync(h_dst, d_src, bytes, cudaMemcpyDeviceToHost, st));
         return;
     }
     constexpr int NB = 3;
@@ -650,8 +658,8 @@ void Model::download_bytes(void *h_dst, const void *d_src, size_t bytes) {
         const int b = i % NB;
         const size_t len = std::min(CHUNK, bytes - off);
         if (busy[b].valid()) busy[b].get();                       // the staging buffer has been emptied
-        FB_CUDA(cudaMemcpyAsync(stage[b], static_cast<const char *>(d_src) + off, len, cudaMemcpyDeviceToHost, st_));
-        FB_CUDA(cudaEventRecord(ev[b], st_));
+        FB_CUDA(cudaMemcpyAsync(stage[b], static_cast<const char *>(d_src) + off, len, cudaMemcpyDeviceToHost, st));
+        FB_CUDA(cudaEventRecord(ev[b], st));
         char *dst = static_cast<char *>(h_dst) + off; const char *src = static_cast<const char *>(stage[b]); cudaEvent_t e = ev[b];
         busy[b] = std::async(std::launch::async, [=] {
             cudaEventSynchronize(e);
@@ -784,9 +792,16 @@ void Model::run_signal(const fb_params *p, fb_signal_out *out) {
     }
     double *early_h[4] = {out->phihat, out->weight, out->biasmat, out->decaymat};
     bool early = !std::getenv("FB_NO_EARLY_DOWNLOAD") && (early_h[0] || early_h[1] || early_h[2] || early_h[3]);
-    for (double *h : early_h) if (h && !host_pinned(h)) early = false;
+    // pinned buffers take plain asynchronous copies; pageable ones (R vectors) the staged copy of download_bytes, run by a
+    // second host thread while this one drives the solves; a mix of the two gets no early copies
+    int n_pinned = 0, n_pageable = 0;
+    for (double *h : early_h) if (h) { if (host_pinned(h)) ++n_pinned; else ++n_pageable; }
+    if (n_pinned && n_pageable) early = false;
+    const bool early_staged = early && n_pageable > 0;
+    if (early_staged && (size_t)N * sizeof(double) < stage_min_bytes()) early = false;
     unsigned early_step = 0;                 // the signal step whose early copies are in the caller's buffers (0: none)
     struct DlGuard { cudaStream_t s; ~DlGuard() { if (s) cudaStreamSynchronize(s); } } dl_guard{early ? st_dl_ : nullptr};
+    std::future<void> early_task;            // early_staged: joins in its destructor, before the buffers above go
     for (unsigned step = 1; step <= p->nouter; ++step) {
         check_interrupt();
         if (p->verbose) std::printf("step %u", step);
@@ -806,7 +821,10 @@ void Model::run_signal(const fb_params *p, fb_signal_out *out) {
             if (partial) FB_CUDA(cudaMemcpyAsync(tab_sig_.p, tab_.p, tab_.n * sizeof(double), cudaMemcpyDeviceToDevice, st_));
             sig_partial = partial;
             kernel_launches += 1;
-            if (early && (current_tol_val <= tol_val * 1.01 || step == p->nouter) && cudaEventQuery(ev_dl_) == cudaSuccess) {
+            const bool early_idle = early_staged ? (!early_task.valid() || early_task.wait_for(std::chrono::seconds(0)) == std::future_status::ready)
+                                                 : cudaEventQuery(ev_dl_) == cudaSuccess;
+            if (early && (current_tol_val <= tol_val * 1.01 || step == p->nouter) && early_idle) {
+                if (early_task.valid()) early_task.get();
                 FB_CUDA(cudaEventRecord(ev_in_, st_));
                 FB_CUDA(cudaStreamWaitEvent(st_dl_, ev_in_, 0));
                 if (dcol[1] || dcol[2]) {
@@ -815,10 +833,25 @@ void Model::run_signal(const fb_params *p, fb_signal_out *out) {
                 }
                 FB_CUDA(cudaEventRecord(ev_sk_, st_dl_));
                 const double *src[4] = {partial ? nullptr : phihat_.p, partial ? nullptr : wgt_.p, dcol[1], dcol[2]};
-                for (int c = 0; c < 4; ++c)
-                    if (early_h[c] && src[c])
-                        FB_CUDA(cudaMemcpyAsync(early_h[c], src[c], (size_t)N * sizeof(double), cudaMemcpyDeviceToHost, st_dl_));
-                FB_CUDA(cudaEventRecord(ev_dl_, st_dl_));
+                if (!early_staged) {
+                    for (int c = 0; c < 4; ++c)
+                        if (early_h[c] && src[c])
+                            FB_CUDA(cudaMemcpyAsync(early_h[c], src[c], (size_t)N * sizeof(double), cudaMemcpyDeviceToHost, st_dl_));
+                    FB_CUDA(cudaEventRecord(ev_dl_, st_dl_));
+                } else {
+                    int dev = 0;
+                    FB_CUDA(cudaGetDevice(&dev));
+                    double *d0 = early_h[0], *d1 = early_h[1], *d2 = early_h[2], *d3 = early_h[3];
+                    const double *s0 = src[0], *s1 = src[1], *s2 = src[2], *s3 = src[3];
+                    early_task = std::async(std::launch::async, [this, dev, N, d0, d1, d2, d3, s0, s1, s2, s3] {
+                        FB_CUDA(cudaSetDevice(dev));
+                        double *dst[4] = {d0, d1, d2, d3};
+                        const double *s4[4] = {s0, s1, s2, s3};
+                        for (int c = 0; c < 4; ++c)
+                            if (dst[c] && s4[c]) download_bytes(dst[c], s4[c], (size_t)N * sizeof(double), st_dl_);
+                        FB_CUDA(cudaStreamSynchronize(st_dl_));
+                    });
+                }
                 early_step = step;
             }
             for (int d = 0; d < D; ++d) {
@@ -875,9 +908,11 @@ void Model::run_signal(const fb_params *p, fb_signal_out *out) {
         // the early copies stand when the loop ended on the signal step that made them
         const bool have_early = early_step != 0 && early_step == (unsigned)out->nsteps;
         const auto tail0 = std::chrono::steady_clock::now();
-        const bool early_landed = early_step != 0 && cudaEventQuery(ev_dl_) == cudaSuccess;
+        const bool early_landed = early_step != 0 && (early_staged ? early_task.wait_for(std::chrono::seconds(0)) == std::future_status::ready
+                                                                    : cudaEventQuery(ev_dl_) == cudaSuccess);
         const bool have_yw = have_early && !sig_partial;
-        if (early_step) FB_CUDA(cudaStreamWaitEvent(st_, ev_dl_, 0));     // biasmat / decaymat are written again below
+        if (early_task.valid()) early_task.get();                          // staged early copies: all in the caller's buffers
+        else if (early_step) FB_CUDA(cudaStreamWaitEvent(st_, ev_dl_, 0)); // biasmat / decaymat are written again below
         // the patch numbers (six kernels per dataset) on the second stream, under the column downloads of this one
         if (early && out->patchno && host_pinned(out->patchno)) {
             FB_CUDA(cudaEventRecord(ev_in_, st_));

@@ -120,7 +120,7 @@ private:
     void check_interrupt();
     void patchnos(const double *d_value, double tol, bool compute, int32_t *h_out);
     void download(double *h_dst, const double *d_src, size_t n);
-    void download_bytes(void *h_dst, const void *d_src, size_t bytes);
+    void download_bytes(void *h_dst, const void *d_src, size_t bytes, cudaStream_t st = nullptr);   // nullptr: the handle's stream
     void upload_bytes(void *d_dst, const void *h_src, size_t bytes);
 };
 

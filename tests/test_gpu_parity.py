@@ -543,11 +543,12 @@ def test_pipelined_pageable_copies_change_nothing(oracle):
         "with cuda_lib().create(mat, 700) as h:\n"
         "    o = h.run_signal(0.5, 2.5, 0.05)\n"
         "print(' '.join(str(zlib.crc32(np.ascontiguousarray(o[k]).tobytes())) for k in\n"
-        "      ('log_signal', 'phihat', 'weight', 'signal', 'binless', 'background', 'patchno')))\n" % ROOT)
+        "      ('log_signal', 'phihat', 'weight', 'biasmat', 'decaymat', 'signal', 'binless', 'background', 'patchno')))\n" % ROOT)
     outs = []
-    for env_extra in ({}, {"FB_STAGE_MIN_MB": "1"}):
+    # staged + the early copies of phihat / weight / biasmat / decaymat by a second host thread (fb_run_signal), then without
+    for env_extra in ({}, {"FB_STAGE_MIN_MB": "1"}, {"FB_STAGE_MIN_MB": "1", "FB_NO_EARLY_DOWNLOAD": "1"}):
         env = dict(os.environ); env.pop("FB_STAGE_MIN_MB", None); env.update(env_extra)
         r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=env, timeout=300)
         assert r.returncode == 0, r.stderr[-2000:]
         outs.append(r.stdout.strip().splitlines()[-1])
-    assert outs[0] == outs[1]
+    assert outs[0] == outs[1] == outs[2]
