@@ -38,6 +38,16 @@ __attribute__((optimize("O3"))) bool row_is_layout(const int32_t *__restrict__ p
     return bad == 0;
 }
 
+// name[k] == d1, bin1[k] == i1, bin2[k] == i1 + k for every k < len (columns that are absent are not looked at)
+__attribute__((optimize("O3"))) bool row_is_ordered(const int32_t *__restrict__ nm, const int32_t *__restrict__ b1,
+                                                    const int32_t *__restrict__ b2, const int32_t d1, const int32_t i1, const int64_t len) {
+    int bad = 0;
+    if (nm) for (int64_t k = 0; k < len; ++k) bad |= (nm[k] != d1);
+    if (b1) for (int64_t k = 0; k < len; ++k) bad |= (b1[k] != i1);
+    if (b2) for (int64_t k = 0; k < len; ++k) bad |= (b2[k] != i1 + (int32_t)k);
+    return bad == 0;
+}
+
 const char *kLayoutMsg = "pos1/pos2 do not depend on the bin only or distance not on bin2-bin1 only";   // -> per-cell fallback
 const char *kSizeMsg = "Input size should be N(N+1)/2 dense matrix of observed counts for each dataset";
 
@@ -245,6 +255,10 @@ void Model::ingest(int nbins, const fb_mat *m) {
             std::atomic<bool> range_bad{false};
             const char *e = par_rows(D, [&](int64_t d, int64_t i) -> const char * {
                 const int64_t base = d * ncells + rm_start(i, n);
+                // the usual case, a row at a time without branches; a row that fails is walked again for the message
+                if (row_is_ordered(m->name ? m->name + base : nullptr, m->bin1 ? m->bin1 + base : nullptr,
+                                   m->bin2 ? m->bin2 + base : nullptr, (int32_t)(d + 1), (int32_t)(i + 1), n - i))
+                    return nullptr;
                 for (int64_t j = i; j < n; ++j) {
                     const int64_t g = base + (j - i);
                     if (m->bin1 && (m->bin1[g] < 1 || m->bin1[g] > n)) { range_bad = true; return "range"; }
