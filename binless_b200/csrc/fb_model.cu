@@ -605,9 +605,6 @@ SolverPool &solver_pool() {
 
 void release_idle_solvers() { solver_pool().clear(); }
 
-// The fused-lasso object of a call: a FRESH FusedLassoGaussianEstimator<GFLLibrary> in the reference (fast_binless.cpp:122).
-// Its structure (chain batches, the captured ADMM graph, the device arrays) depends on (nbins, maxdiag) only, so the handle
-// keeps one and hands it out reset to the cold state (beta = z = u = 0, alpha = 5, counters 0).
 // the handle's solver goes to the pool (idle, its stream drained) or, when it is shared between GPUs, away
 void Model::retire_solver() {
     if (!flo_) return;
@@ -621,6 +618,10 @@ void Model::retire_solver() {
     flo_.reset();
 }
 
+// The fused-lasso object of a call: a FRESH FusedLassoGaussianEstimator<GFLLibrary> in the reference (fast_binless.cpp:122).
+// Its structure (chain batches, the captured ADMM graph, the device arrays) depends on (nbins, maxdiag) only, so the handle
+// keeps one (or takes an idle one of that shape from the pool) and hands it out reset to the cold state
+// (beta = z = u = 0, alpha = 5, counters 0).
 GflSolver &Model::solver(unsigned maxdiag) {
     if (!flo_ || flo_maxdiag_ != maxdiag || flo_comm_ != (Comm::get().active() ? Comm::get().world() : 1)) {
         retire_solver();
