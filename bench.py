@@ -245,7 +245,10 @@ def run_cuda(args):
                    "l2": "inputs larger than L2 (working set > 1 GB per call)", "units_per_rank": 1,
                    "host": {"cpus": os.cpu_count(), "numa_node_of_rank0_gpu": numa, "host_threads_per_rank": os.environ.get("FB_HOST_THREADS")}},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
-                "ms_per_step": t_e2e / args.steps * 1e3},
+                "ms_per_step": t_e2e / args.steps * 1e3,
+                "what": "fb_create (validation + H2D) + fb_run_signal + fb_destroy per step, pinned host buffers; every output column "
+                        "is copied to the host inside the call: phihat / weight / biasmat / decaymat on a second stream while the "
+                        "last solves run, the rest after them (FB_NO_EARLY_DOWNLOAD=1: all after)"},
         "e2e_pageable": {"value": pg_value, "unit": UNIT, "ms_per_step": t_pg / 2 * 1e3, "steps": 2,
                          "what": "numpy (pageable) host buffers, name / bin1 / bin2 passed and validated: what the Rcpp shim supplies"},
         "gpu_launches": int(launches),

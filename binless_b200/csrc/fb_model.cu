@@ -108,6 +108,15 @@ void write_signal_csv(const char *path, int64_t N, const double *const cols[7]) 
                  !(e && std::atoi(e) != 0));
 }
 
+// has everything recorded before `e` finished? (a "not ready" answer must not stay behind as the thread's last CUDA error)
+bool event_done(cudaEvent_t e) {
+    const cudaError_t r = cudaEventQuery(e);
+    if (r == cudaSuccess) return true;
+    cudaGetLastError();
+    if (r != cudaErrorNotReady) throw CudaError(std::string("cudaEventQuery: ") + cudaGetErrorString(r));
+    return false;
+}
+
 // true for host memory the driver can DMA into directly (cudaHostAlloc / cudaHostRegister / managed)
 bool host_pinned(const void *p) {
     cudaPointerAttributes at{};
@@ -837,7 +846,7 @@ void Model::run_signal(const fb_params *p, fb_signal_out *out) {
             sig_partial = partial;
             kernel_launches += 1;
             const bool early_idle = early_staged ? (!early_task.valid() || early_task.wait_for(std::chrono::seconds(0)) == std::future_status::ready)
-                                                 : cudaEventQuery(ev_dl_) == cudaSuccess;
+                                                 : event_done(ev_dl_);
             if (early && (current_tol_val <= tol_val * 1.01 || step == p->nouter) && early_idle) {
                 if (early_task.valid()) early_task.get();
                 FB_CUDA(cudaEventRecord(ev_in_, st_));
@@ -924,7 +933,7 @@ void Model::run_signal(const fb_params *p, fb_signal_out *out) {
         const bool have_early = early_step != 0 && early_step == (unsigned)out->nsteps;
         const auto tail0 = std::chrono::steady_clock::now();
         const bool early_landed = early_step != 0 && (early_staged ? early_task.wait_for(std::chrono::seconds(0)) == std::future_status::ready
-                                                                    : cudaEventQuery(ev_dl_) == cudaSuccess);
+                                                                    : event_done(ev_dl_));
         const bool have_yw = have_early && !sig_partial;
         if (early_task.valid()) early_task.get();                          // staged early copies: all in the caller's buffers
         else if (early_step) FB_CUDA(cudaStreamWaitEvent(st_, ev_dl_, 0)); // biasmat / decaymat are written again below
