@@ -117,6 +117,13 @@ bool event_done(cudaEvent_t e) {
     return false;
 }
 
+int host_threads();
+// host threads that move one staging chunk (FB_STAGE_THREADS; default: up to 8 of the process's host threads)
+int stage_threads() {
+    if (const char *e = std::getenv("FB_STAGE_THREADS")) return std::max(1, std::min(64, std::atoi(e)));
+    return std::max(1, std::min(8, host_threads()));
+}
+
 // true for host memory the driver can DMA into directly (cudaHostAlloc / cudaHostRegister / managed)
 bool host_pinned(const void *p) {
     cudaPointerAttributes at{};
@@ -676,7 +683,7 @@ void Model::download_bytes(void *h_dst, const void *d_src, size_t bytes, cudaStr
     constexpr int NB = 3;
     void *stage[NB]; cudaEvent_t ev[NB]; std::future<void> busy[NB];
     for (int b = 0; b < NB; ++b) { stage[b] = BlockCache::host().get(CHUNK); FB_CUDA(cudaEventCreateWithFlags(&ev[b], cudaEventDisableTiming)); }
-    const int nthr = std::max(1, std::min(8, host_threads()));
+    const int nthr = stage_threads();
     size_t off = 0;
     for (int i = 0; off < bytes; ++i, off += CHUNK) {
         const int b = i % NB;
@@ -714,7 +721,7 @@ void Model::upload_bytes(void *d_dst, const void *h_src, size_t bytes) {
     constexpr int NB = 3;
     void *stage[NB]; cudaEvent_t ev[NB]; bool used[NB] = {false, false, false};
     for (int b = 0; b < NB; ++b) { stage[b] = BlockCache::host().get(CHUNK); FB_CUDA(cudaEventCreateWithFlags(&ev[b], cudaEventDisableTiming)); }
-    const int nthr = std::max(1, std::min(8, host_threads()));
+    const int nthr = stage_threads();
     size_t off = 0;
     for (int i = 0; off < bytes; ++i, off += CHUNK) {
         const int b = i % NB;
