@@ -164,6 +164,7 @@ void Model::open_stream() {
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
         throw CudaError("no CUDA device available (there is no CPU fallback)");
+    FB_CUDA(cudaGetDevice(&dev_));
     FB_CUDA(cudaStreamCreateWithFlags(&st_, cudaStreamNonBlocking));
     FB_CUDA(cudaEventCreate(&ev0_));
     FB_CUDA(cudaEventCreate(&ev1_));
@@ -625,10 +626,9 @@ void release_idle_solvers() { solver_pool().clear(); }
 void Model::retire_solver() {
     if (!flo_) return;
     if (!flo_->sharded() && st_) {
-        int dev = 0;
-        if (cudaStreamSynchronize(st_) == cudaSuccess && cudaGetDevice(&dev) == cudaSuccess) {
+        if (cudaStreamSynchronize(st_) == cudaSuccess) {
             flo_->rebind(nullptr);
-            solver_pool().give(dev, t_.n, flo_maxdiag_, std::move(flo_));
+            solver_pool().give(dev_, t_.n, flo_maxdiag_, std::move(flo_));
         }
     }
     flo_.reset();
@@ -641,9 +641,7 @@ void Model::retire_solver() {
 GflSolver &Model::solver(unsigned maxdiag) {
     if (!flo_ || flo_maxdiag_ != maxdiag || flo_comm_ != (Comm::get().active() ? Comm::get().world() : 1)) {
         retire_solver();
-        int dev = 0;
-        FB_CUDA(cudaGetDevice(&dev));
-        if (!Comm::get().active()) flo_ = solver_pool().take(dev, t_.n, maxdiag);
+        if (!Comm::get().active()) flo_ = solver_pool().take(dev_, t_.n, maxdiag);
         if (flo_) { flo_->rebind(st_); flo_->reset(); }
         else flo_.reset(new GflSolver(t_.n, maxdiag, st_));
         flo_maxdiag_ = maxdiag; flo_comm_ = Comm::get().active() ? Comm::get().world() : 1;

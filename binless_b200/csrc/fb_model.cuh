@@ -57,6 +57,7 @@ public:
 private:
     Tri t_;
     cudaStream_t st_ = nullptr;
+    int dev_ = 0;                     // the device the handle lives on (current at construction)
     cudaEvent_t ev0_ = nullptr, ev1_ = nullptr;
     // early download of the output columns that are final before the last fused-lasso solves (run_signal): a second stream
     cudaStream_t st_dl_ = nullptr;
