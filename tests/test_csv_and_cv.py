@@ -37,6 +37,32 @@ def test_gzip_csv_equals_reference_text(product_lib, oracle_port, tmp_path, nrow
         assert len(raw) < len(want)
 
 
+def test_csv_values_print_like_printf(product_lib, oracle_port, tmp_path):
+    """The product prints "%.4f" with its own exact integer arithmetic (fb_csv.cpp: fmt_fixed4), the oracle with the C
+    library like the reference's ostream. Ties at the fifth decimal (k / 32: 10^4 / 32 = 312.5), values next to them,
+    subnormals, signed zeros, huge values and non-finite ones must give the same characters."""
+    rng = np.random.default_rng(7)
+    ties = rng.integers(0, 100000, 20000) + (2 * rng.integers(0, 16, 20000) + 1) / 32.0
+    near = rng.integers(0, 10 ** 9, 20000) / 10000.0 + 0.00005
+    mags = np.ldexp(1.0 + rng.random(20000), rng.integers(-60, 70, 20000))
+    bits = rng.integers(0, 2 ** 63 - 1, 20000, dtype=np.int64).view(np.float64)
+    bits = bits[np.isfinite(bits)]
+    special = np.array([0.0, -0.0, 5e-324, -5e-324, 2.2250738585072014e-308, 0.03125, -0.03125, 0.09375, 0.99995, 9999.99995,
+                        1125899906842623.9, 1125899906842624.0, 1e15, 1e16, 1e22, 1e300, -1e300, np.inf, -np.inf, np.nan,
+                        0.5, 1.00005, 2.00005, 3.00015, 123456.78125])
+    x = np.concatenate([special, ties, -ties, near, np.nextafter(near, 0), np.nextafter(near, 1e30), mags, -mags, bits])
+    fp, fo = str(tmp_path / "p.csv"), str(tmp_path / "o.csv")
+    product_lib.csv_write(fp, '"x"', [x], gzip=False)
+    oracle_port.csv_write(fo, '"x"', [x], gzip=False)
+    got, want = open(fp, "rb").read().split(b"\n"), open(fo, "rb").read().split(b"\n")
+    assert len(got) == len(want) == x.size + 2
+    bad = [(float(x[k - 1]), got[k], want[k]) for k in range(1, x.size + 1) if got[k] != want[k]]
+    assert not bad, bad[:5]
+    # and against Python's own correctly rounded formatting, for the finite ones
+    for k in range(special.size, special.size + 2000):
+        assert got[k + 1] == ("%.4f" % x[k]).encode()
+
+
 def test_gzip_csv_many_slabs(product_lib, oracle_port, tmp_path):
     """more rows than one formatting slab (2^20): the pieces of all slabs form ONE deflate stream"""
     n = (1 << 20) + 12345
