@@ -978,7 +978,7 @@ void Model::run_signal(const fb_params *p, fb_signal_out *out) {
             const double *src[7] = {phihat_.p, wgt_.p, dcol[1], dcol[2], dcol[3], dcol[4], dcol[0]};
             const double *hc[7];
             for (int c = 0; c < 7; ++c) {
-                FB_CUDA(cudaMemcpyAsync(hbuf.data() + (size_t)c * N, src[c], N * sizeof(double), cudaMemcpyDeviceToHost, st_));
+                download(hbuf.data() + (size_t)c * N, src[c], N);     // pageable: staged and pipelined when large
                 hc[c] = hbuf.data() + (size_t)c * N;
             }
             FB_CUDA(cudaStreamSynchronize(st_));
